@@ -1,0 +1,118 @@
+/* se_b200.h -- C ABI of libse_b200.so: the B200 (sm_100a) STFT / complex-conv / mask hot path.
+ *
+ * The reference (shs2783/Speech-Enhancement) is pure Python and has no FFI of its own; the
+ * boundary it fixes is the nn.Module surface of four classes.  Each
+ * entry point below is what the Python shim under speech_enhancement_b200/ binds with ctypes
+ * in place of the ATen call the reference makes at the cited line.  Plain pointers and
+ * integers only: no torch types, no libtorch link dependency.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to fp32 (unless the name ends in _bf16), contiguous
+ *     in the layout stated; the library never allocates, frees or synchronises.
+ *   - `stream` is a cudaStream_t passed as void*; launches are asynchronous on it.
+ *   - return value: SE_OK (0) or a negative SE_ERR_* code; se_last_error() gives the message
+ *     of the last failure on the calling thread.
+ */
+#ifndef SE_B200_H_
+#define SE_B200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SE_API __attribute__((visibility("default")))
+#else
+#define SE_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SE_OK                 0
+#define SE_ERR_BAD_ARG       -1   /* null pointer, non-positive size, inconsistent dims      */
+#define SE_ERR_UNSUPPORTED   -2   /* shape / option outside what the kernels implement       */
+#define SE_ERR_CUDA          -3   /* a CUDA runtime or driver call failed (see last_error)    */
+#define SE_ERR_WORKSPACE     -4   /* caller-provided workspace too small                      */
+
+/* mask variants, se_mask_fwd `kind` */
+#define SE_MASK_DCCRN_R        0  /* _2008_00264_dccrn.py:188-190 */
+#define SE_MASK_DCCRN_C        1  /* _2008_00264_dccrn.py:191-193 */
+#define SE_MASK_DCCRN_E        2  /* _2008_00264_dccrn.py:194-205 */
+#define SE_MASK_DCUNET_UNB     3  /* _1903_03107_dcunet.py:159-161 */
+#define SE_MASK_DCUNET_SIGMOID 4  /* _1903_03107_dcunet.py:163-165 */
+#define SE_MASK_DCUNET_TANH    5  /* _1903_03107_dcunet.py:167-182 */
+#define SE_MASK_CARN           6  /* _2104_05267_carn.py:165-166 (sign quirk kept) */
+#define SE_MASK_FRCRN          7  /* _2206_07293_frcrn.py:141-152 */
+
+/* conv engine selector, `engine` argument */
+#define SE_ENGINE_AUTO         0  /* tcgen05 where the shape qualifies, else SIMT fp32       */
+#define SE_ENGINE_SIMT         1  /* CUDA-core fp32 implicit GEMM                            */
+#define SE_ENGINE_UMMA         2  /* tcgen05 bf16x3 split implicit GEMM (error if unsupported)*/
+
+SE_API int         se_version(void);
+SE_API const char* se_last_error(void);
+/* 1 when the current device is compute capability 10.x, 0 otherwise, <0 on CUDA error */
+SE_API int         se_device_ok(void);
+/* number of kernels this library has launched since it was loaded (bench.py gpu_launches) */
+SE_API int64_t     se_launch_count(void);
+
+/* ---- ConvSTFT.forward (conv_stft.py:48-56): reflect pad + F.conv1d(stride=hop) -------------
+ * x [B, L]; W [C2, win] (the module's `weight` buffer, [C2,1,win] contiguous); out [B, C2, T]
+ * with T = (L + 2*pad*center - win)/hop + 1.                                                   */
+SE_API int se_stft_fwd(const float* x, int64_t B, int64_t L, const float* W, int C2, int win, int hop,
+                int pad, int center, float* out, int64_t T, void* stream);
+
+/* ---- return_mag_phase branch (conv_stft.py:58-64): spec [B,2F,T] -> mags, phase [B,F,T] ---- */
+SE_API int se_magphase_fwd(const float* spec, int64_t B, int F, int64_t T, float* mags, float* phase,
+                    void* stream);
+
+/* ---- ConviSTFT.forward (conv_stft.py:96-116) -------------------------------------------------
+ * spec [B, C2, T]  (or mags [B, F, T] when phase != NULL, phase [B, F, T]);
+ * A_packed [hop_pad, J*C2]: the module's inverse basis `weight` [C2, win] regrouped by
+ * se_istft_pack_basis (J = ceil(win/hop));  window [win];
+ * out [B, out_len] = (overlap-add / (coff + 1e-8))[crop_front : crop_front + out_len].         */
+SE_API int se_istft_pack_basis(const float* Winv, int C2, int win, int hop, float* A_packed, void* stream);
+SE_API int se_istft_fwd(const float* spec, const float* phase_or_null, const float* A_packed,
+                 const float* window, int64_t B, int C2, int64_t T, int win, int hop,
+                 int64_t crop_front, int64_t out_len, float* out, void* stream);
+
+/* ---- ComplexConv2d / ComplexConvTranspose2d (complex_nn.py:52-91) ----------------------------
+ * se_cconv_pack_weight: Wr, Wi are the real_conv / imag_conv weights
+ *   (conv: [Co, Ci, kh, kw]; transposed: [Ci, Co, kh, kw]); packed is the real GEMM operand
+ *   [2Co, 2Ci*kh*kw] = [[Wr,-Wi],[Wi,Wr]] with K ordered (ci2, dh, dw); bias_packed [2Co] =
+ *   [br-bi, br+bi] (only written when br, bi != NULL).
+ * se_cconv2d_fwd / se_cconvT2d_fwd: x [B, 2Ci, H, W] -> y [B, 2Co, Ho, Wo], NCHW fp32.        */
+SE_API int se_cconv_pack_weight(const float* Wr, const float* Wi, const float* br, const float* bi,
+                         int Co, int Ci, int kh, int kw, int transposed,
+                         float* packed, float* bias_packed, void* stream);
+SE_API int se_cconv2d_fwd(const float* x, const float* packed, const float* bias_packed_or_null,
+                   int64_t B, int Cin2, int H, int W, int Cout2, int kh, int kw,
+                   int sh, int sw, int ph, int pw, float* y, int Ho, int Wo,
+                   int engine, void* workspace, int64_t workspace_bytes, void* stream);
+SE_API int se_cconvT2d_fwd(const float* x, const float* packed, const float* bias_packed_or_null,
+                    int64_t B, int Cin2, int H, int W, int Cout2, int kh, int kw,
+                    int sh, int sw, int ph, int pw, float* y, int Ho, int Wo,
+                    int engine, void* workspace, int64_t workspace_bytes, void* stream);
+/* bytes of scratch the UMMA engine needs for this problem (0 for SIMT) */
+SE_API int64_t se_cconv_workspace_bytes(int64_t B, int Cin2, int H, int W, int Cout2, int kh, int kw,
+                                 int sh, int sw, int transposed);
+
+/* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
+ * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),
+ * so slices of the STFT output and of the decoder output are consumed in place.  For
+ * SE_MASK_FRCRN the mask planes have F-2 rows.  out [B, 2F, T] contiguous (real | imag).       */
+SE_API int se_mask_fwd(int kind,
+                const float* nr, int64_t nr_bs, int64_t nr_fs,
+                const float* ni, int64_t ni_bs, int64_t ni_fs,
+                const float* mr, int64_t mr_bs, int64_t mr_fs,
+                const float* mi, int64_t mi_bs, int64_t mi_fs,
+                int64_t B, int F, int64_t T, float* out, void* stream);
+
+/* polar -> rectangular (conv_stft.py:96-100): mags, phase [B,F,T] -> spec [B,2F,T] */
+SE_API int se_polar_to_rect(const float* mags, const float* phase, int64_t B, int F, int64_t T,
+                     float* spec, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SE_B200_H_ */

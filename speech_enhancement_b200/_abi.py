@@ -1,0 +1,92 @@
+"""ctypes binding of libse_b200.so (C ABI declared in include/se_b200.h).
+
+There is deliberately NO fallback: if the shared library is missing or a call fails the
+caller gets a RuntimeError.  Tensors are passed as raw device pointers plus sizes; launches
+go on ``torch.cuda.current_stream()`` so they order with surrounding PyTorch ops.
+"""
+import ctypes as C
+import os
+import re
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'csrc', 'libse_b200.so')
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), 'include', 'se_b200.h')
+
+SE_OK, SE_ERR_BAD_ARG, SE_ERR_UNSUPPORTED, SE_ERR_CUDA, SE_ERR_WORKSPACE = 0, -1, -2, -3, -4
+MASK_DCCRN_R, MASK_DCCRN_C, MASK_DCCRN_E = 0, 1, 2
+MASK_DCUNET_UNB, MASK_DCUNET_SIGMOID, MASK_DCUNET_TANH, MASK_CARN, MASK_FRCRN = 3, 4, 5, 6, 7
+ENGINE_AUTO, ENGINE_SIMT, ENGINE_UMMA = 0, 1, 2
+
+_P, _I, _L = C.c_void_p, C.c_int, C.c_int64
+_SIGS = {
+    'se_version': (C.c_int, []),
+    'se_last_error': (C.c_char_p, []),
+    'se_device_ok': (C.c_int, []),
+    'se_launch_count': (C.c_int64, []),
+    'se_stft_fwd': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _I, _I, _P, _L, _P]),
+    'se_magphase_fwd': (C.c_int, [_P, _L, _I, _L, _P, _P, _P]),
+    'se_istft_pack_basis': (C.c_int, [_P, _I, _I, _I, _P, _P]),
+    'se_istft_fwd': (C.c_int, [_P, _P, _P, _P, _L, _I, _L, _I, _I, _L, _L, _P, _P]),
+    'se_cconv_pack_weight': (C.c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P]),
+    'se_cconv2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
+    'se_cconvT2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
+    'se_cconv_workspace_bytes': (C.c_int64, [_L] + [_I] * 9),
+    'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
+    'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),
+}
+
+_lib = None
+
+
+def declared_symbols():
+    """Names of every function prototyped in include/se_b200.h."""
+    with open(HEADER_PATH) as f:
+        return sorted(set(re.findall(r'SE_API\s+[\w\s\*]+?\b(se_\w+)\s*\(', f.read())))
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises RuntimeError when the .so is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f'{LIB_PATH} not found: build it with `python -c "import __graft_entry__ as g; g.build()"` '
+                '(speech_enhancement_b200 has no CPU or PyTorch fallback)')
+        h = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(h, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = h
+    return _lib
+
+
+_EXC = {SE_ERR_BAD_ARG: ValueError, SE_ERR_UNSUPPORTED: RuntimeError, SE_ERR_CUDA: RuntimeError,
+        SE_ERR_WORKSPACE: RuntimeError}
+
+
+def check(rc):
+    if rc != SE_OK:
+        msg = lib().se_last_error().decode(errors='replace')
+        raise _EXC.get(rc, RuntimeError)(f'libse_b200: {msg} (code {rc})')
+
+
+def stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def require_cuda_f32(t, name):
+    """The kernels take fp32 CUDA tensors only (SURVEY.md 8b error conventions)."""
+    if not isinstance(t, torch.Tensor):
+        raise ValueError(f'{name}: expected a torch.Tensor, got {type(t).__name__}')
+    if not t.is_cuda:
+        raise RuntimeError(f'{name}: speech_enhancement_b200 runs on CUDA (sm_100a) only; got a '
+                           f'{t.device.type} tensor and there is no CPU fallback')
+    if t.dtype != torch.float32:
+        raise RuntimeError(f'{name}: only float32 is supported, got {t.dtype}')
+    return t

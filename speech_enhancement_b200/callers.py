@@ -1,0 +1,324 @@
+"""Caller models of the hot path: DCCRN, DCUNet, FRCRN hosts written for this package.
+
+The reference's model files (/root/reference/models/_2008_00264_dccrn.py, _1903_03107_dcunet.py,
+_2206_07293_frcrn.py) are the callers of the hot path; they can be used unchanged through
+`dropin.install()`.  These hosts exist so that bench / smoke / tests run on a box without the
+reference checkout.  They keep the reference's constructor arguments, forward contract
+`model(wav[B,L]) -> (spec[B,2F,T], wav[B,L'])` and state_dict keys (so reference checkpoints
+load), and differ in one respect: the inline mask math + torch.cat is one fused kernel call.
+
+`ops` selects the implementation of the hot-path pieces (ConvSTFT, ConviSTFT, ComplexConv2d,
+ComplexConvTranspose2d, mask functions).  The default is the CUDA implementation of this
+package; the CPU oracle passes its own namespace to obtain the timed CPU baseline.
+"""
+import types
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .modules.complex_nn import complex_concat, split_complex, merge_real_imag
+from .modules.complex_aux import ComplexBatchNorm2d, ComplexLSTM, ComplexLinear
+
+
+def cuda_ops():
+    from . import conv_stft, functional
+    from .modules import complex_nn
+    return types.SimpleNamespace(
+        ConvSTFT=conv_stft.ConvSTFT, ConviSTFT=conv_stft.ConviSTFT,
+        ComplexConv2d=complex_nn.ComplexConv2d, ComplexConvTranspose2d=complex_nn.ComplexConvTranspose2d,
+        mask_dccrn=functional.mask_dccrn, mask_dcunet=functional.mask_dcunet,
+        mask_frcrn=functional.mask_frcrn, mask_carn=functional.mask_carn)
+
+
+class _Block(nn.Module):
+    """(causal time pad) -> complex conv / convT -> complex BN -> activation.
+
+    dccrn.py:11-57, frcrn.py:12-59 (causal=True pads `time_pad` frames on the left before the
+    layer, :29 / :53), dcunet.py:13-43 (no explicit pad)."""
+
+    def __init__(self, ops, transposed, cin, cout, kernel, act, norm=True, time_pad=0, **kw):
+        super().__init__()
+        layer = (ops.ComplexConvTranspose2d if transposed else ops.ComplexConv2d)(
+            cin, cout, kernel, bias=not norm, **kw)
+        setattr(self, 'conv_transposed' if transposed else 'conv', layer)
+        self._layer_name = 'conv_transposed' if transposed else 'conv'
+        self.norm = ComplexBatchNorm2d(cout) if norm else nn.Identity()
+        self.act = act if act is not None else nn.Identity()
+        self.time_pad = time_pad
+
+    def forward(self, x):
+        if self.time_pad:
+            x = F.pad(x, (self.time_pad, 0, 0, 0))
+        return self.act(self.norm(getattr(self, self._layer_name)(x)))
+
+
+class _Stack(nn.Module):
+    def __init__(self, layers):
+        super().__init__()
+        self.layers = nn.ModuleList(layers)
+
+
+def _spec_planes(spec, n_bins):
+    return spec[:, :n_bins, :], spec[:, n_bins:, :]
+
+
+# ------------------------------------------------------------------------------------ DCCRN
+class _LSTMBlock(nn.Module):
+    """dccrn.py:59-86: (num_layers) ComplexLSTM + ComplexLinear."""
+
+    def __init__(self, cin, hidden, linear, num_layers=2, **kw):
+        super().__init__()
+        ndir = 2 if kw.get('bidirectional', True) else 1
+        mods = [ComplexLSTM(cin, hidden, num_layers=1, **kw) for _ in range(num_layers - 1)]
+        mods += [ComplexLSTM(ndir * hidden, hidden, num_layers=1, **kw), ComplexLinear(ndir * hidden, linear)]
+        self.layers = nn.ModuleList(mods)
+
+    def forward(self, x):
+        for layer in self.layers:
+            x = layer(x)
+        return x
+
+
+class DCCRN(nn.Module):
+    """DCCRN-R/C/E/CL (dccrn.py:123-212)."""
+
+    def __init__(self, config='dccrn-CL', window_size=400, hop_size=100, fft_size=512, lstm_channels=256,
+                 linear_channels=1024, bidirectional=False, is_complex=True, ops=None):
+        super().__init__()
+        if not is_complex:
+            raise RuntimeError('DCCRN host: only the complex variant is on the accelerated path')
+        ops = ops or cuda_ops()
+        self._ops = ops
+        if config in ('dccrn-C', 'dccrn-R', 'dccrn-E'):
+            enc, self.masking = [32, 64, 128, 128, 256, 256], config[-1]
+        else:
+            enc, self.masking = [32, 64, 128, 256, 256, 256], 'E'
+        dec = enc[:-1][::-1] + [2]
+        self.fft_size = fft_size
+        self.stft = ops.ConvSTFT(window_size, hop_size, fft_size)
+        self.istft = ops.ConviSTFT(window_size, hop_size, fft_size)
+        chans = [2] + enc
+        self.encoder = _Stack([_Block(ops, False, chans[i], chans[i + 1], (5, 2), nn.PReLU(), time_pad=1,
+                                      stride=(2, 1), padding=(2, 0)) for i in range(len(enc))])
+        cin, layers = 256, []
+        for cout in dec:
+            layers.append(_Block(ops, True, cin * 2, cout, (5, 2), nn.PReLU(), time_pad=0,
+                                 stride=(2, 1), padding=(2, 0), output_padding=(1, 0)))
+            cin = cout
+        self.decoder = _Stack(layers)
+        freq = fft_size // 2 // (2 ** len(enc)) * enc[-1]
+        self.lstm = _LSTMBlock(freq, lstm_channels, linear_channels, num_layers=2, batch_first=True,
+                               bidirectional=bidirectional)
+
+    def forward(self, x):
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)                                               # [B, 2F, T]
+        noisy_real, noisy_imag = _spec_planes(spec, n_bins)
+        x = torch.stack([noisy_real, noisy_imag], dim=1)[:, :, 1:, :]      # drop DC (:155-156)
+        skips = []
+        for layer in self.encoder.layers:
+            x = layer(x)
+            skips.append(x)
+        b, c, f, t = x.shape
+        x = self.lstm(x.reshape(b, c * f, t).permute(0, 2, 1))
+        x = x.permute(0, 2, 1).reshape(b, c, f, t)
+        for layer in self.decoder.layers:
+            skip = skips.pop()
+            if x.shape[-1] > skip.shape[-1]:
+                x = x[..., :-1]
+            x = layer(complex_concat([x, skip], dim=1))
+        x = F.pad(x, (0, 0, 1, 0))                                        # zero DC row (:169)
+        mask_real, mask_imag = x[:, 0], x[:, 1]
+        if mask_real.shape[-1] > noisy_real.shape[-1]:
+            mask_real, mask_imag = mask_real[..., :-1], mask_imag[..., :-1]
+        est_spec = self._ops.mask_dccrn(self.masking, noisy_real, noisy_imag, mask_real, mask_imag)
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp_(wav, -1, 1)
+
+
+# ------------------------------------------------------------------------------------ DCUNet
+# (complex channels, kernel, stride, padding) per encoder layer, architectures.py:53-99
+_K75, _K53 = (7, 5), (5, 3)
+DCUNET_LAYERS = {
+    'dcunet10': [(32, _K75, (2, 2), (3, 2)), (64, _K75, (2, 2), (3, 2)), (64, _K53, (2, 2), (2, 1)),
+                 (64, _K53, (2, 2), (2, 1)), (64, _K53, (2, 1), (2, 1))],
+    'dcunet16': [(32, _K75, (2, 2), (3, 2)), (32, _K75, (2, 1), (3, 2)), (64, _K75, (2, 2), (3, 2))]
+                + [(64, _K53, s, (2, 1)) for s in ((2, 1), (2, 2), (2, 1), (2, 2), (2, 1))],
+    'dcunet20': [(32, (7, 1), (1, 1), (3, 0)), (32, (1, 7), (1, 1), (0, 3)), (64, _K75, (2, 2), (3, 2)),
+                 (64, _K75, (2, 1), (3, 2))]
+                + [(64, _K53, s, (2, 1)) for s in ((2, 2), (2, 1), (2, 2), (2, 1), (2, 2))]
+                + [(90, _K53, (2, 1), (2, 1))],
+    'dcunet20-large': [(45, (7, 1), (1, 1), (3, 0)), (45, (1, 7), (1, 1), (0, 3)), (90, _K75, (2, 2), (3, 2)),
+                       (90, _K75, (2, 1), (3, 2))]
+                      + [(90, _K53, s, (2, 1)) for s in ((2, 2), (2, 1), (2, 2), (2, 1), (2, 2))]
+                      + [(128, _K53, (2, 1), (2, 1))],
+}
+
+
+class DCUNet(nn.Module):
+    """DCUNet-10/16/20/20-large (dcunet.py:98-189)."""
+
+    def __init__(self, config, window_size=512, hop_size=128, fft_size=512, normalize=False, is_complex=True,
+                 ops=None):
+        super().__init__()
+        if not is_complex:
+            raise RuntimeError('DCUNet host: only the complex variant is on the accelerated path')
+        ops = ops or cuda_ops()
+        self._ops = ops
+        arch = DCUNET_LAYERS[config]
+        self.window_size, self.hop_size, self.fft_size, self.normalize = window_size, hop_size, fft_size, normalize
+        self.stft = ops.ConvSTFT(window_size, hop_size, fft_size)
+        self.istft = ops.ConviSTFT(window_size, hop_size, fft_size)
+        lrelu = lambda: nn.LeakyReLU(0.01)
+        c0 = arch[0][0] * 2
+        self.first_conv = _Block(ops, False, 2, c0, 3, lrelu(), padding=1)
+        enc, cin = [], c0
+        for ch, k, s, p in arch:
+            enc.append(_Block(ops, False, cin, ch * 2, k, lrelu(), stride=s, padding=p))
+            cin = ch * 2
+        self.encoder = _Stack(enc)
+        dec = []
+        for i in range(len(arch) - 1):                                    # dcunet.py:72-78
+            _, k, s, p = arch[-i - 1]
+            cout = arch[-i - 2][0] * 2
+            dec.append(_Block(ops, True, cin * 2, cout, k, lrelu(), stride=s, padding=p))
+            cin = cout
+        _, k, s, p = arch[0]
+        dec.append(_Block(ops, True, cin * 2, 2, k, None, stride=s, padding=p))
+        self.decoder = _Stack(dec)
+
+    def forward(self, x):
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)
+        real, imag = _spec_planes(spec, n_bins)
+        cs = torch.stack([real, imag], dim=1)
+        if self.normalize:                                                # dcunet.py:127-130
+            mean = torch.mean(cs, dim=[1, 2, 3], keepdim=True)
+            std = torch.std(cs, dim=[1, 2, 3], keepdim=True)
+            cs = (cs - mean) / (std + 1e-8)
+        x = self.first_conv(cs)
+        skips = []
+        for layer in self.encoder.layers:
+            x = layer(x)
+            skips.append(x)
+        for layer in self.decoder.layers:
+            skip = skips.pop()
+            if skip.shape != x.shape:                                     # dcunet.py:89-92
+                x = F.pad(x, (0, abs(skip.shape[3] - x.shape[3]), 0, abs(skip.shape[2] - x.shape[2])))
+            x = layer(torch.cat([x, skip], dim=1))
+        x = x[:, :, :cs.shape[2], :cs.shape[3]]                           # dcunet.py:141-146
+        est_spec = self._ops.mask_dcunet('bounded_tanh', cs[:, 0], cs[:, 1], x[:, 0], x[:, 1])
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp_(wav, -1, 1)
+
+
+# ------------------------------------------------------------------------------------ FRCRN
+class _LinearBlock(nn.Module):
+    def __init__(self, cin, cout, act):
+        super().__init__()
+        self.linear = ComplexLinear(cin, cout, bias=False)
+        self.act = nn.ReLU() if act else nn.Identity()
+
+    def forward(self, x):
+        return self.act(self.linear(x))
+
+
+class _ChannelAttention(nn.Module):
+    """ccbam.py:28-63: avg/max pooled descriptors -> shared complex MLP -> sigmoid."""
+
+    def __init__(self, channels, r=16):
+        super().__init__()
+        red = channels // r if channels // r else 2
+        self.shared_fc_layer = nn.Sequential(_LinearBlock(channels, red, True), _LinearBlock(red, channels, False))
+
+    def forward(self, x):
+        b, c = x.shape[:2]
+        avg = self.shared_fc_layer(x.mean(dim=(2, 3)))     # [real | imag] order == channel order
+        mx = self.shared_fc_layer(x.amax(dim=(2, 3)))
+        return torch.sigmoid(avg + mx).view(b, c, 1, 1)
+
+
+class _SpatialAttention(nn.Module):
+    """ccbam.py:65-86: channel-pooled maps -> 7x7 complex conv + CBN + ReLU -> sigmoid."""
+
+    def __init__(self, ops):
+        super().__init__()
+        self.conv = _Block(ops, False, 4, 2, 7, nn.ReLU(), padding=3)
+
+    def forward(self, x):
+        real, imag = split_complex(x)
+        pooled = torch.cat([real.mean(1, keepdim=True), real.amax(1, keepdim=True),
+                            imag.mean(1, keepdim=True), imag.amax(1, keepdim=True)], dim=1)
+        return torch.sigmoid(self.conv(pooled))
+
+
+class CCBAM(nn.Module):
+    """complex convolutional block attention (ccbam.py:88-106)."""
+
+    def __init__(self, feature_map_channels, reduction=16, ops=None):
+        super().__init__()
+        ops = ops or cuda_ops()
+        self.channel_attention_branch = _ChannelAttention(feature_map_channels, reduction)
+        self.spatial_attention_branch = _SpatialAttention(ops)
+
+    def forward(self, x):
+        x = x * self.channel_attention_branch(x)
+        sa = self.spatial_attention_branch(x)
+        real, imag = split_complex(x)
+        return merge_real_imag(x, real + sa[:, 0:1], imag + sa[:, 1:2], dim=1)
+
+
+class _FrcrnDecoder(nn.Module):
+    def __init__(self, ops, channels=128, repeats=6, reduction=16):
+        super().__init__()
+        self.skip_connection_attention_layers = nn.ModuleList(
+            [CCBAM(channels, reduction, ops=ops) for _ in range(repeats)])
+        self.layers = nn.ModuleList(
+            [_Block(ops, True, channels * 2, channels, (5, 2), nn.LeakyReLU(0.2), time_pad=0,
+                    stride=(2, 1), padding=(0, 0)) for _ in range(repeats)])
+
+
+class FRCRN(nn.Module):
+    """FRCRN without FSMN (frcrn.py:104-155)."""
+
+    def __init__(self, window_size=320, hop_size=160, fft_size=640, lstm_channels=256, reduction_ratio=16,
+                 is_complex=True, ops=None):
+        super().__init__()
+        if not is_complex:
+            raise RuntimeError('FRCRN host: only the complex variant is on the accelerated path')
+        ops = ops or cuda_ops()
+        self._ops = ops
+        self.fft_size = fft_size
+        self.stft = ops.ConvSTFT(window_size, hop_size, fft_size)
+        self.istft = ops.ConviSTFT(window_size, hop_size, fft_size)
+        chans = [2] + [128] * 6
+        self.encoder = _Stack([_Block(ops, False, chans[i], chans[i + 1], (5, 2), nn.LeakyReLU(0.2), time_pad=1,
+                                      stride=(2, 1), padding=(0, 0)) for i in range(6)])
+        self.decoder = _FrcrnDecoder(ops, 128, 6, reduction_ratio)
+        self.lstm = ComplexLSTM(256, lstm_channels, num_layers=2, bidirectional=False, batch_first=True)
+        self.final_conv = nn.Conv2d(128, 2, kernel_size=(1, 2), bias=False)
+
+    def forward(self, x):
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)
+        noisy_real, noisy_imag = _spec_planes(spec, n_bins)
+        x = torch.stack([noisy_real, noisy_imag], dim=1)[:, :, 1:, :]
+        skips = []
+        for layer in self.encoder.layers:
+            x = layer(x)
+            skips.append(x)
+        b, c, f, t = x.shape
+        x = self.lstm(x.reshape(b, c * f, t).permute(0, 2, 1))
+        x = x.permute(0, 2, 1).reshape(b, c, f, t)
+        for att, layer in zip(self.decoder.skip_connection_attention_layers, self.decoder.layers):
+            skip = att(skips.pop())
+            if x.shape[-1] > skip.shape[-1]:
+                x = x[..., :-1]
+            if x.shape[-2] < skip.shape[-2]:
+                x = F.pad(x, (0, 0, 0, 1))
+            x = layer(complex_concat([x, skip], dim=1))
+        x = self.final_conv(x)                                            # [B, 2, F-2, T]
+        est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, x[:, 0], x[:, 1])
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp_(wav, -1, 1)
