@@ -40,8 +40,10 @@ class ComplexLSTM(nn.Module):
         # both inputs share each LSTM's weights: run them stacked on the batch axis (2 calls, not 4)
         bdim = 0 if self.real_lstm.batch_first else 1
         both = torch.cat([real, imag], dim=bdim)
-        by_real, _ = self.real_lstm(both)
-        by_imag, _ = self.imag_lstm(both)
+        # cuDNN RNNs default to TF32 math on CUDA; the parity target is the fp32 reference
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            by_real, _ = self.real_lstm(both)
+            by_imag, _ = self.imag_lstm(both)
         r2r, i2r = torch.chunk(by_real, 2, dim=bdim)
         r2i, i2i = torch.chunk(by_imag, 2, dim=bdim)
         return merge_real_imag(x, r2r - i2i, r2i + i2r, dim=-1)

@@ -62,7 +62,9 @@ def test_stft_input_forms_and_not_centered():
         assert spec.shape == g['nc_spec'].shape and rel_l2(spec.cpu(), g['nc_spec']) < TOL_EXACT
         assert torch.equal(spec, st(x[None, None, :])) and torch.equal(spec, st(x[None, :]))
         wav = ist(spec)
-        assert wav.shape == g['nc_wav'].shape and rel_l2(wav.cpu(), g['nc_wav']) < TOL_EXACT
+        # without centring the first/last samples divide by window^2 ~ 0 (+1e-8): ill-conditioned edges
+        assert wav.shape == g['nc_wav'].shape and rel_l2(wav.cpu(), g['nc_wav']) < 1e-4
+        assert rel_l2(wav[:, 100:-100].cpu(), g['nc_wav'][:, 100:-100]) < TOL_EXACT
     with pytest.raises(RuntimeError):
         se.ConvSTFT(400, 100, 512).to(DEV)(torch.zeros(1, 100, device=DEV))     # reflect pad > signal
 
