@@ -114,6 +114,61 @@ def test_cconv_golden_auto(i):
     assert rel_l2(y.cpu(), g[f'{name}_y']) < 2e-4
 
 
+@pytest.mark.parametrize('i', range(len(CONV_CASES)))
+def test_cconv_golden_umma(i):
+    """every golden geometry forced through the tcgen05 bf16x3 engine (module tolerance 2e-4;
+    the split keeps ~16 mantissa bits per operand so the observed error is ~1e-5)"""
+    g = golden('cconv')
+    name, m, x, y = _conv_case(i, _abi.ENGINE_UMMA)
+    assert y.shape == g[f'{name}_y'].shape
+    err = rel_l2(y.cpu(), g[f'{name}_y'])
+    assert err < 2e-4, err
+
+
+# (transposed, cin, cout, kernel, kwargs, H, W, B): real layer shapes of SURVEY.md 8a
+LAYER_SHAPES = [
+    (False, 32, 64, (5, 2), dict(stride=(2, 1), padding=(2, 0)), 128, 643, 2),          # DCCRN enc1
+    (False, 128, 256, (5, 2), dict(stride=(2, 1), padding=(2, 0)), 32, 643, 1),         # DCCRN enc3
+    (False, 256, 256, (5, 2), dict(stride=(2, 1), padding=(2, 0)), 8, 643, 2),          # DCCRN enc5
+    (True, 512, 256, (5, 2), dict(stride=(2, 1), padding=(2, 0), output_padding=(1, 0)), 4, 642, 2),   # dec0
+    (True, 256, 64, (5, 2), dict(stride=(2, 1), padding=(2, 0), output_padding=(1, 0)), 32, 642, 1),   # dec3
+    (True, 64, 2, (5, 2), dict(stride=(2, 1), padding=(2, 0), output_padding=(1, 0)), 128, 642, 1),    # dec5
+    (False, 64, 128, (7, 5), dict(stride=(2, 2), padding=(3, 2)), 257, 501, 1),         # DCUNet enc2
+    (False, 128, 180, (5, 3), dict(stride=(2, 1), padding=(2, 1)), 3, 32, 3),           # DCUNet enc9 (N=192)
+    (True, 360, 128, (5, 3), dict(stride=(2, 1), padding=(2, 1)), 2, 32, 3),            # DCUNet dec0
+    (True, 256, 128, (5, 3), dict(stride=(2, 2), padding=(2, 1)), 9, 63, 2),            # DCUNet dec3
+    (True, 128, 64, (1, 7), dict(stride=(1, 1), padding=(0, 3)), 65, 126, 1),           # DCUNet dec8-like
+    (True, 256, 128, (5, 2), dict(stride=(2, 1), padding=(0, 0)), 37, 403, 1),          # FRCRN dec3
+]
+
+
+@pytest.mark.parametrize('case', range(len(LAYER_SHAPES)))
+def test_cconv_layer_shapes_umma_vs_simt_and_oracle(case):
+    transposed, cin, cout, k, kw, H, W, B = LAYER_SHAPES[case]
+    m = (se.ComplexConvTranspose2d if transposed else se.ComplexConv2d)(cin, cout, k, bias=False, **kw)
+    sd = {key: rand(v.shape, 300 + case * 7 + j, (2.0 / (cin * 5)) ** 0.5)
+          for j, (key, v) in enumerate(sorted(m.state_dict().items()))}
+    m.load_state_dict(sd)
+    x_cpu = rand((B, cin, H, W), 7000 + case)
+    m.to(DEV)
+    x = x_cpu.to(DEV)
+    with torch.no_grad():
+        m.engine = _abi.ENGINE_SIMT
+        y_simt = m(x)
+        m.engine = _abi.ENGINE_UMMA
+        y_umma = m(x)
+        fn = oracle.cconvT2d_ref if transposed else oracle.cconv2d_ref
+        args = dict(stride=kw['stride'], padding=kw['padding'])
+        if transposed:
+            args['output_padding'] = kw.get('output_padding', 0)
+        y_ref = fn(x_cpu.double(), sd['real_conv.weight'].double(), sd['imag_conv.weight'].double(), **args)
+    assert y_umma.shape == y_ref.shape
+    assert rel_l2(y_simt.cpu(), y_ref) < 1e-5
+    err = rel_l2(y_umma.cpu(), y_ref)
+    assert err < 5e-5, err
+    assert torch.isfinite(y_umma).all()
+
+
 def test_cconv_container_forms_and_repack():
     m = se.ComplexConv2d(8, 8, (3, 2), padding=(1, 0)).to(DEV)
     x = rand((2, 8, 9, 7), 1).to(DEV)
