@@ -1,0 +1,48 @@
+"""dropin.install(): the reference's UNMODIFIED model files bind to this package's classes
+(SURVEY.md 8b "Module names").  Needs /root/reference, so it runs in the authoring container only
+and is skipped on the GPU box; runs in a subprocess because it edits sys.modules."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+REF = '/root/reference'
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CODE = r'''
+import sys, warnings
+warnings.filterwarnings('ignore')
+sys.path.insert(0, %r)
+import numpy as np
+import speech_enhancement_b200 as se
+from speech_enhancement_b200 import dropin
+names = dropin.install(%r)
+assert set(names) == {'conv_stft', 'models.conv_stft', 'modules.complex_nn', 'models.modules.complex_nn'}
+import _2008_00264_dccrn as dccrn, _1903_03107_dcunet as dcunet, _2206_07293_frcrn as frcrn
+import _2104_05267_carn as carn, _1809_01405_crn as crn
+g = np.load(%r)
+for name, model in (('dccrn_cl', dccrn.DCCRN('dccrn-CL', 400, 100, 512)),
+                    ('dcunet20', dcunet.DCUNet('dcunet20', 512, 128, 512)),
+                    ('frcrn', frcrn.FRCRN(320, 160, 640))):
+    assert type(model.stft) is se.ConvSTFT and type(model.istft) is se.ConviSTFT, name
+    convs = [m for m in model.modules() if isinstance(m, (se.ComplexConv2d, se.ComplexConvTranspose2d))]
+    assert len(convs) >= 12, (name, len(convs))
+    assert not any(type(m).__module__.startswith('modules.') and 'ComplexConv' in type(m).__name__
+                   for m in model.modules())
+    assert sorted(model.state_dict().keys()) == list(g[name + '_keys']), name
+assert type(carn.CARN(320, 160, 512).stft) is se.ConvSTFT
+assert type(crn.CRN(320, 160, 320).stft) is se.ConvSTFT
+import models                                   # the package-relative names resolve to the same classes
+assert models.ConvSTFT is se.ConvSTFT and models.ComplexConv2d is se.ComplexConv2d
+dropin.uninstall()
+assert 'conv_stft' not in sys.modules
+print('dropin ok')
+'''
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason='reference checkout not present on this machine')
+def test_reference_models_bind_to_this_package():
+    code = CODE % (ROOT, REF, os.path.join(ROOT, 'tests', 'golden', 'models.npz'))
+    res = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and 'dropin ok' in res.stdout, res.stdout[-2000:] + res.stderr[-4000:]

@@ -170,7 +170,7 @@ def test_cconv_layer_shapes_umma_vs_simt_and_oracle(case):
 
 
 def test_cconv_container_forms_and_repack():
-    m = se.ComplexConv2d(8, 8, (3, 2), padding=(1, 0)).to(DEV)
+    m = se.ComplexConv2d(8, 8, (3, 2), padding=(1, 0), bias=False).to(DEV)
     x = rand((2, 8, 9, 7), 1).to(DEV)
     with torch.no_grad():
         y = m(x)
