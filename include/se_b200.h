@@ -97,6 +97,50 @@ SE_API int se_cconvT2d_fwd(const float* x, const float* packed, const float* bia
 SE_API int64_t se_cconv_workspace_bytes(int64_t B, int Cin2, int H, int W, int Cout2, int kh, int kw,
                                  int sh, int sw, int transposed);
 
+/* ---- tcgen05 conv engine, chainable form ------------------------------------------------------
+ * Activations travel between layers in "CL2": channels-last bf16 hi|lo planes [B][2][H][W][Cp]
+ * (value = hi + lo, Cp = channels padded to a multiple of 64, pad channels zero).
+ *   se_cl2_from_nchw / se_cl2_to_nchw   convert the nn.Module layout (NCHW fp32) to / from CL2.
+ *   se_cconv_prep_weight                packed fp32 [Cout2][Cin2][taps] (se_cconv_pack_weight) ->
+ *                                       bf16 hi|lo GEMM operand [taps][2][npad][Cp_total]; chan_map[col]
+ *                                       names the module input channel behind GEMM column `col`
+ *                                       (-1 = padding, NULL = identity) so that one layer can read
+ *                                       its K dimension from two CL2 tensors (decoder input + skip,
+ *                                       complex_nn.py:4-16 complex_concat / torch.cat) without a copy.
+ *   se_cconv_gemm                       the layer itself; replaces complex_nn.py:52-65 (+ the caller's
+ *                                       causal F.pad, _2008_00264_dccrn.py:29, through pad_left).   */
+typedef struct se_cconv_args {
+  int transposed;              /* 0: ComplexConv2d, 1: ComplexConvTranspose2d                      */
+  int64_t B;
+  int nsrc;                    /* 1 or 2 CL2 sources concatenated along K                           */
+  const void* src[2];          /* bf16 [B][2][Hpitch][Wpitch][Cp]                                   */
+  int src_Cp[2];
+  int src_Hpitch[2], src_Wpitch[2];   /* allocated rows / pixels per row (>= H, W)                  */
+  int H, W;                    /* logical input extent read from every source                       */
+  int pad_top, pad_left;       /* zero rows / columns the caller would F.pad before the layer (conv only) */
+  int Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo;
+  const void* wq;              /* from se_cconv_prep_weight, Cp_total = src_Cp[0] (+ src_Cp[1])     */
+  const float* bias;           /* [Cout2] or NULL                                                   */
+  float slope;                 /* epilogue activation v > 0 ? v : slope * v   (1 = none)            */
+  float* y_nchw;               /* [B][Cout2][Ho][Wo] fp32 or NULL                                   */
+  void* y_cl2;                 /* bf16 [B][2][Ho][Wo][y_Cp] or NULL                                 */
+  int y_Cp;
+} se_cconv_args;
+SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);
+SE_API int se_cl2_to_nchw(const void* cl2, int64_t B, int C, int H, int W, int Cp, float* y, void* stream);
+SE_API int64_t se_cconv_wq_elems(int Cout2, int Cp_total, int taps);
+SE_API int se_cconv_prep_weight(const float* packed, int Cout2, int Cin2, int taps, const int* chan_map,
+                                int Cp_total, void* wq, void* stream);
+SE_API int se_cconv_gemm(const se_cconv_args* args, void* stream);
+/* First encoder layer (2 input channels, K = Cin2*kh*kw <= 20: HBM-bound): direct
+ * fp32 kernel reading the input in place through strides (elements; w contiguous) -- e.g. the real
+ * and imaginary row blocks of the STFT output with the DC bin skipped (_2008_00264_dccrn.py:152-156)
+ * and the causal frame pad (:29) -- and writing NCHW fp32 and/or CL2.  Forward convolution only.   */
+SE_API int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, int64_t xs_h, int64_t B, int Cin2,
+                              int H, int W, int pad_top, int pad_left, const float* packed, const float* bias,
+                              float slope, int Cout2, int kh, int kw, int sh, int sw, int ph, int pw,
+                              float* y_nchw, void* y_cl2, int y_Cp, int Ho, int Wo, void* stream);
+
 /* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
  * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),
  * so slices of the STFT output and of the decoder output are consumed in place.  For

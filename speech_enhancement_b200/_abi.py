@@ -33,9 +33,29 @@ _SIGS = {
     'se_cconv2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
     'se_cconvT2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
     'se_cconv_workspace_bytes': (C.c_int64, [_L] + [_I] * 9),
+    'se_cl2_from_nchw': (C.c_int, [_P, _L, _I, _I, _I, _P, _I, _P]),
+    'se_cl2_to_nchw': (C.c_int, [_P, _L, _I, _I, _I, _I, _P, _P]),
+    'se_cconv_wq_elems': (C.c_int64, [_I, _I, _I]),
+    'se_cconv_prep_weight': (C.c_int, [_P, _I, _I, _I, _P, _I, _P, _P]),
+    'se_cconv_gemm': (C.c_int, [_P, _P]),
+    'se_cconv_small_cin': (C.c_int, [_P, _L, _L, _L, _L, _I, _I, _I, _I, _I, _P, _P, C.c_float] + [_I] * 7
+                           + [_P, _P, _I, _I, _I, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),
 }
+
+
+
+class ConvArgs(C.Structure):
+    """mirror of `se_cconv_args` (include/se_b200.h)"""
+    _fields_ = [('transposed', C.c_int), ('B', C.c_int64), ('nsrc', C.c_int), ('src', C.c_void_p * 2),
+                ('src_Cp', C.c_int * 2), ('src_Hpitch', C.c_int * 2), ('src_Wpitch', C.c_int * 2),
+                ('H', C.c_int), ('W', C.c_int), ('pad_top', C.c_int), ('pad_left', C.c_int),
+                ('Cout2', C.c_int), ('kh', C.c_int), ('kw', C.c_int), ('sh', C.c_int), ('sw', C.c_int),
+                ('ph', C.c_int), ('pw', C.c_int), ('Ho', C.c_int), ('Wo', C.c_int),
+                ('wq', C.c_void_p), ('bias', C.c_void_p), ('slope', C.c_float), ('y_nchw', C.c_void_p),
+                ('y_cl2', C.c_void_p), ('y_Cp', C.c_int)]
+
 
 _lib = None
 

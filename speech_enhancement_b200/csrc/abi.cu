@@ -60,6 +60,14 @@ static int cconv_dispatch(bool transposed, const float* x, const float* packed, 
                "%s: output size does not match geometry (output_padding must be < stride)", nm);
   if (B == 0) return SE_OK;
   se::ConvGeom g{Cin2, H, W, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo};
+  if (engine == SE_ENGINE_AUTO) {
+    // degenerate layers are HBM-bound: direct fp32 kernels
+    if (!transposed && Cin2 <= 8 && Cin2 * kh * kw <= 512 && Ho <= 65535 && B <= 65535)
+      return se_cconv_small_cin(x, (int64_t)Cin2 * H * W, (int64_t)H * W, W, B, Cin2, H, W, 0, 0, packed, bias, 1.f,
+                                Cout2, kh, kw, sh, sw, ph, pw, y, nullptr, 0, Ho, Wo, stream);
+    if (Cout2 <= 4 && kh * kw * Cin2 <= 12800 && Ho <= 65535 && B <= 65535)
+      return se::cconv_fwd_small_cout(transposed, x, packed, bias, B, g, y, (cudaStream_t)stream);
+  }
   if (engine == SE_ENGINE_UMMA || (engine == SE_ENGINE_AUTO && se::cconv_umma_supported(transposed, B, g))) {
     return se::cconv_fwd_umma(transposed, x, packed, bias, B, g, y, ws, ws_bytes, (cudaStream_t)stream);
   }

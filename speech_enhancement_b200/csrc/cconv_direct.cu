@@ -1,0 +1,219 @@
+// Direct (CUDA-core) kernels for the degenerate complex-conv layers that are HBM-bound by
+// construction: the first encoder layer of every model has 2 input channels
+// (K = Cin2*kh*kw <= 20), so its cost is writing the output once.  One thread owns one output
+// pixel, keeps <= 32 output channels in registers per pass, reads the packed fp32 weights as
+// shared-memory broadcasts and stores either NCHW fp32 (module contract) or CL2 bf16 hi|lo (chain).
+// Reference semantics: complex_nn.py:52-78 through the packed operand [[Wr,-Wi],[Wi,Wr]].
+#include "engines.cuh"
+#include <cuda_bf16.h>
+
+namespace se {
+
+struct SmallCinParams {
+  const float* x; int64_t xs_b, xs_c, xs_h;      // input strides in elements (w contiguous)
+  int Cin2, H, W, pad_top, pad_left;
+  int Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo;
+  const float* w;                                 // packed [Cout2][Cin2*kh*kw]
+  const float* bias; float slope;
+  float* y; __nv_bfloat16* y_cl2; int y_Cp;
+};
+
+constexpr int kSmallCinMaxK = 512;
+
+__global__ void __launch_bounds__(128)
+cconv_small_cin_kernel(const SmallCinParams p) {
+  extern __shared__ float w_s[];                  // [K][Cout2r]  (Cout2 rounded up to 32)
+  const int K = p.Cin2 * p.kh * p.kw;
+  const int Cr = (p.Cout2 + 31) / 32 * 32;
+  for (int i = threadIdx.x; i < K * Cr; i += blockDim.x) {
+    int k = i / Cr, co = i - k * Cr;
+    w_s[i] = co < p.Cout2 ? __ldg(p.w + (int64_t)co * K + k) : 0.f;
+  }
+  __syncthreads();
+  const int wo = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ho = blockIdx.y;
+  const int64_t b = blockIdx.z;
+  if (wo >= p.Wo) return;
+  const int64_t plane = (int64_t)p.Ho * p.Wo;
+  const int64_t pix = (int64_t)ho * p.Wo + wo;
+  const int cmax = p.y_cl2 != nullptr && p.y_Cp > Cr ? p.y_Cp : Cr;
+  for (int c0 = 0; c0 < cmax; c0 += 32) {
+    float acc[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+    if (c0 < Cr) {
+      // walk the K = Cin2*kh*kw taps; inputs come from L1 after the first pass (zero padding + the
+      // caller's causal pad are the bounds checks)
+      int k = 0;
+      for (int c = 0; c < p.Cin2; ++c)
+        for (int dh = 0; dh < p.kh; ++dh) {
+          const int h = ho * p.sh - p.ph - p.pad_top + dh;
+          const bool h_ok = h >= 0 && h < p.H;
+          const float* xr = p.x + b * p.xs_b + c * p.xs_c + (int64_t)h * p.xs_h;
+          for (int dw = 0; dw < p.kw; ++dw, ++k) {
+            const int w = wo * p.sw - p.pw - p.pad_left + dw;
+            const float xk = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + w) : 0.f;
+            const float4* wr = reinterpret_cast<const float4*>(w_s + k * Cr + c0);
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 w4 = wr[j4];
+              acc[4 * j4 + 0] = fmaf(w4.x, xk, acc[4 * j4 + 0]);
+              acc[4 * j4 + 1] = fmaf(w4.y, xk, acc[4 * j4 + 1]);
+              acc[4 * j4 + 2] = fmaf(w4.z, xk, acc[4 * j4 + 2]);
+              acc[4 * j4 + 3] = fmaf(w4.w, xk, acc[4 * j4 + 3]);
+            }
+          }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int co = c0 + j;
+      float f = acc[j];
+      if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
+      acc[j] = co < p.Cout2 ? (f > 0.f ? f : f * p.slope) : 0.f;
+    }
+    if (p.y != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc[j];
+    }
+    if (p.y_cl2 != nullptr && c0 < p.y_Cp) {
+      __align__(16) __nv_bfloat16 hi[32];
+      __align__(16) __nv_bfloat16 lo[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        hi[j] = __float2bfloat16_rn(acc[j]);
+        lo[j] = __float2bfloat16_rn(acc[j] - __bfloat162float(hi[j]));
+      }
+      __nv_bfloat16* cb = p.y_cl2 + (b * 2 * plane + pix) * p.y_Cp + c0;
+      uint4* dh = reinterpret_cast<uint4*>(cb);
+      uint4* dl = reinterpret_cast<uint4*>(cb + plane * p.y_Cp);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        dh[j] = reinterpret_cast<const uint4*>(hi)[j];
+        dl[j] = reinterpret_cast<const uint4*>(lo)[j];
+      }
+    }
+  }
+}
+
+}  // namespace se
+
+extern "C" int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, int64_t xs_h, int64_t B, int Cin2,
+                                  int H, int W, int pad_top, int pad_left, const float* packed, const float* bias,
+                                  float slope, int Cout2, int kh, int kw, int sh, int sw, int ph, int pw,
+                                  float* y_nchw, void* y_cl2, int y_Cp, int Ho, int Wo, void* stream) {
+  SE_REQUIRE(x && packed && (y_nchw || y_cl2), "se_cconv_small_cin: null pointer");
+  SE_REQUIRE(B >= 0 && Cin2 > 0 && Cout2 > 0 && H > 0 && W > 0 && kh > 0 && kw > 0 && sh > 0 && sw > 0 &&
+             Ho > 0 && Wo > 0 && pad_top >= 0 && pad_left >= 0, "se_cconv_small_cin: bad geometry");
+  SE_REQUIRE(Ho == (H + pad_top + 2 * ph - kh) / sh + 1 && Wo == (W + pad_left + 2 * pw - kw) / sw + 1,
+             "se_cconv_small_cin: output size does not match geometry");
+  SE_REQUIRE(y_cl2 == nullptr || (y_Cp >= Cout2 && y_Cp % 64 == 0), "se_cconv_small_cin: bad y_Cp");
+  const int K = Cin2 * kh * kw, Cr = (Cout2 + 31) / 32 * 32;
+  if (K > se::kSmallCinMaxK || (size_t)K * Cr * 4 > 160 * 1024)
+    return se::fail(SE_ERR_UNSUPPORTED, "se_cconv_small_cin: needs Cin2*kh*kw <= %d", se::kSmallCinMaxK);
+  if (B == 0) return SE_OK;
+  if (Ho > 65535 || B > 65535) return se::fail(SE_ERR_UNSUPPORTED, "se_cconv_small_cin: tensor too large");
+  se::SmallCinParams p{x, xs_b, xs_c, xs_h, Cin2, H, W, pad_top, pad_left, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo,
+                       packed, bias, slope, y_nchw, reinterpret_cast<__nv_bfloat16*>(y_cl2), y_Cp};
+  const int smem = K * Cr * 4;
+  static int smem_attr = 48 * 1024;
+  if (smem > smem_attr) {
+    SE_CUDA(cudaFuncSetAttribute(se::cconv_small_cin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    smem_attr = smem;
+  }
+  dim3 grid((unsigned)((Wo + 127) / 128), (unsigned)Ho, (unsigned)B);
+  se::cconv_small_cin_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(p);
+  return se::check_launch("se_cconv_small_cin");
+}
+
+// ---- last decoder layer: Cout2 <= 4 (M = 2 in SURVEY.md 8a), cost = reading the input once ----
+namespace se {
+
+struct SmallCoutParams {
+  const float* x; const float* w; const float* bias; float* y;
+  int transposed, Cin2, H, W, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo;
+  float slope;
+};
+
+// one thread per output pixel; weights in shared memory as float4 per (tap, cin): [taps][Cin2][4]
+__global__ void __launch_bounds__(128)
+cconv_small_cout_kernel(const SmallCoutParams p) {
+  extern __shared__ float4 w4_s[];
+  const int taps = p.kh * p.kw;
+  for (int i = threadIdx.x; i < taps * p.Cin2; i += blockDim.x) {
+    const int tap = i / p.Cin2, c = i - tap * p.Cin2;
+    float v[4];
+#pragma unroll
+    for (int co = 0; co < 4; ++co)
+      v[co] = co < p.Cout2 ? __ldg(p.w + ((int64_t)co * p.Cin2 + c) * taps + tap) : 0.f;
+    w4_s[i] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __syncthreads();
+  const int wo = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ho = blockIdx.y;
+  const int64_t b = blockIdx.z;
+  if (wo >= p.Wo) return;
+  const int64_t in_plane = (int64_t)p.H * p.W;
+  const float* xb = p.x + b * p.Cin2 * in_plane;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int dh = 0; dh < p.kh; ++dh) {
+    int hi;
+    if (p.transposed) {
+      const int nh = ho + p.ph - dh;
+      if (nh < 0 || nh % p.sh != 0) continue;
+      hi = nh / p.sh;
+    } else {
+      hi = ho * p.sh - p.ph + dh;
+    }
+    if (hi < 0 || hi >= p.H) continue;
+    for (int dw = 0; dw < p.kw; ++dw) {
+      int wi;
+      if (p.transposed) {
+        const int nw = wo + p.pw - dw;
+        if (nw < 0 || nw % p.sw != 0) continue;
+        wi = nw / p.sw;
+      } else {
+        wi = wo * p.sw - p.pw + dw;
+      }
+      if (wi < 0 || wi >= p.W) continue;
+      const float* xp = xb + (int64_t)hi * p.W + wi;
+      const float4* wp = w4_s + (dh * p.kw + dw) * p.Cin2;
+#pragma unroll 8
+      for (int c = 0; c < p.Cin2; ++c) {
+        const float xv = __ldg(xp + c * in_plane);
+        const float4 w = wp[c];
+        acc.x = fmaf(w.x, xv, acc.x); acc.y = fmaf(w.y, xv, acc.y);
+        acc.z = fmaf(w.z, xv, acc.z); acc.w = fmaf(w.w, xv, acc.w);
+      }
+    }
+  }
+  const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
+  const int64_t plane = (int64_t)p.Ho * p.Wo;
+#pragma unroll
+  for (int co = 0; co < 4; ++co) {
+    if (co >= p.Cout2) break;
+    float f = a4[co] + (p.bias ? __ldg(p.bias + co) : 0.f);
+    p.y[(b * p.Cout2 + co) * plane + (int64_t)ho * p.Wo + wo] = f > 0.f ? f : f * p.slope;
+  }
+}
+
+int cconv_fwd_small_cout(bool transposed, const float* x, const float* packed, const float* bias, int64_t B,
+                         const ConvGeom& g, float* y, cudaStream_t s) {
+  const int smem = g.kh * g.kw * g.Cin2 * 16;
+  if (g.Cout2 > 4 || smem > 200 * 1024)
+    return fail(SE_ERR_UNSUPPORTED, "small-Cout direct kernel: needs Cout2 <= 4 and kh*kw*Cin2 <= 12800");
+  if (g.Ho > 65535 || B > 65535) return fail(SE_ERR_UNSUPPORTED, "small-Cout direct kernel: tensor too large");
+  SmallCoutParams p{x, packed, bias, y, transposed ? 1 : 0, g.Cin2, g.H, g.W, g.Cout2, g.kh, g.kw, g.sh, g.sw,
+                    g.ph, g.pw, g.Ho, g.Wo, 1.f};
+  static int smem_attr = 48 * 1024;
+  if (smem > smem_attr) {
+    SE_CUDA(cudaFuncSetAttribute(cconv_small_cout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    smem_attr = smem;
+  }
+  dim3 grid((unsigned)((g.Wo + 127) / 128), (unsigned)g.Ho, (unsigned)B);
+  cconv_small_cout_kernel<<<grid, 128, smem, s>>>(p);
+  return check_launch("cconv_small_cout_kernel");
+}
+
+}  // namespace se

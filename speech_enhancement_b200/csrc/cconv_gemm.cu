@@ -1,0 +1,724 @@
+// tcgen05 / TMEM / TMA engine for ComplexConv2d and ComplexConvTranspose2d
+// (reference semantics: /root/reference/models/modules/complex_nn.py:52-91).
+//
+// One real implicit GEMM per layer against the packed operand [[Wr,-Wi],[Wi,Wr]]:
+//     D[pixel, cout2] = sum_{tap} sum_{cin2} X[pixel (+) tap, cin2] * Wp[tap][cout2, cin2]
+// fp32 accuracy on bf16 tensor cores through a 3-term split: x = x_hi + x_lo (both bf16),
+//     x*w ~= x_lo*w_hi + x_hi*w_lo + x_hi*w_hi          (fp32 accumulate in TMEM)
+//
+// Activation format ("CL2"): channels-last bf16 hi|lo planes  [B][2][H][W][Cp]  (Cp = C padded to
+// 64).  Strided convolutions read it through TMA *element strides* (the box walks every sh-th row /
+// sw-th pixel), zero padding is TMA out-of-bounds fill, a transposed convolution is run as sh*sw
+// stride-1 sub-convolutions (output parity classes) so no multiply by an inserted zero is issued.
+// The epilogue can emit NCHW fp32 (the nn.Module contract) and/or CL2 for the next layer, with the
+// folded bias and a leaky activation applied, so a chain of layers never leaves this format.
+//
+// What bounds the kernel is L2->SMEM fill (measured ~38 B/cycle/SM), not the tensor pipe, so the
+// CTA tile is shaped to reuse every byte it stages:
+//   * A (activations): taps that differ only by a row offset share ONE halo box
+//     [nacc*TH + span rows][TW][kb]; each tap's MMA reads it through a row-shifted descriptor.
+//   * B (weights): one [npad x kb] slab per tap feeds `nacc` accumulators (vertically stacked
+//     128-pixel sub-tiles, nacc*npad <= 512 TMEM columns).
+//   * A and B travel in separate mbarrier rings (2 A slots, up to 6 B slots).
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + tcgen05.mma issuer,
+// warps 2-5 = epilogue (tcgen05.ld -> bias/activation -> NCHW fp32 and/or CL2 bf16 stores).
+#include "engines.cuh"
+#include "umma.cuh"
+#include <cuda_bf16.h>
+#include <cmath>
+#include <cstdlib>
+
+namespace se {
+
+constexpr int kMaxTaps = 49;
+constexpr int kMaxGroups = 48;
+constexpr int kMaxClasses = 4;
+constexpr int kSmemBudget = 226 * 1024;      // dynamic smem we allow ourselves incl. alignment slack (227 KB limit)
+
+struct GTap { uint16_t arow, wslab; };
+struct GGroup { int16_t row_add, col_add; uint8_t src, ntaps, tap0, pad_; };
+struct GClass {
+  int Hq_out, Wq_out, oh_mul, oh_add, ow_mul, ow_add;
+  int g0, ng, tiles_h, tiles_w, tile_begin;
+};
+
+struct GemmParams {
+  GClass cls[kMaxClasses];
+  GGroup groups[kMaxGroups];
+  GTap taps[kMaxTaps];
+  int ncls, row_mul, col_mul;
+  int kblocks[2], kcol0[2];
+  int TH, TW, nacc;
+  int concat, acc_cols;       // concat: a_hi x [b_hi|b_lo] in one MMA (npad <= 128), 2*npad TMEM columns per accumulator
+  int a_half, a_slot, b_unit, SA, SB;
+  int Ho, Wo, Cout2, npad, tmem_cols, y_Cp;
+  const float* bias;
+  float slope;
+  float* y;
+  __nv_bfloat16* y_cl2;
+};
+
+// ------------------------------------------------------------------------------ prep kernels
+__device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(v);
+  lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
+// NCHW fp32 -> CL2.  grid: (ceil(W/32), H, B*(Cp/64)); block 256
+__global__ void __launch_bounds__(256)
+cl2_from_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xs, int C, int H, int W, int Cp) {
+  __shared__ __align__(16) __nv_bfloat16 s_hi[32][64 + 8];
+  __shared__ __align__(16) __nv_bfloat16 s_lo[32][64 + 8];
+  const int cblocks = Cp / 64;
+  const int cb = blockIdx.z % cblocks, b = blockIdx.z / cblocks;
+  const int h = blockIdx.y, w0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const bool pix_ok = (w0 + tx) < W;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int cl = ty + 8 * i, c = cb * 64 + cl;
+    float v = (pix_ok && c < C) ? __ldg(x + (((int64_t)b * C + c) * H + h) * W + w0 + tx) : 0.f;
+    split_bf16(v, s_hi[tx][cl], s_lo[tx][cl]);
+  }
+  __syncthreads();
+  const int pix = threadIdx.x >> 3, chunk = threadIdx.x & 7;
+  if (w0 + pix < W) {
+    const int64_t plane = (int64_t)H * W * Cp;
+    int64_t off = ((int64_t)h * W + w0 + pix) * Cp + cb * 64 + chunk * 8;
+    *reinterpret_cast<uint4*>(xs + ((int64_t)b * 2 + 0) * plane + off) = *reinterpret_cast<const uint4*>(&s_hi[pix][chunk * 8]);
+    *reinterpret_cast<uint4*>(xs + ((int64_t)b * 2 + 1) * plane + off) = *reinterpret_cast<const uint4*>(&s_lo[pix][chunk * 8]);
+  }
+}
+
+// CL2 -> NCHW fp32 (hi + lo).  grid: (ceil(W/32), H, B*(Cp/64)); block 256
+__global__ void __launch_bounds__(256)
+cl2_to_nchw_kernel(const __nv_bfloat16* __restrict__ xs, float* __restrict__ y, int C, int H, int W, int Cp) {
+  __shared__ float s[32][64 + 1];
+  const int cblocks = Cp / 64;
+  const int cb = blockIdx.z % cblocks, b = blockIdx.z / cblocks;
+  const int h = blockIdx.y, w0 = blockIdx.x * 32;
+  const int pix = threadIdx.x >> 3, chunk = threadIdx.x & 7;
+  if (w0 + pix < W) {
+    const int64_t plane = (int64_t)H * W * Cp;
+    int64_t off = ((int64_t)h * W + w0 + pix) * Cp + cb * 64 + chunk * 8;
+    uint4 hi = *reinterpret_cast<const uint4*>(xs + ((int64_t)b * 2 + 0) * plane + off);
+    uint4 lo = *reinterpret_cast<const uint4*>(xs + ((int64_t)b * 2 + 1) * plane + off);
+    const __nv_bfloat16* ph = reinterpret_cast<const __nv_bfloat16*>(&hi);
+    const __nv_bfloat16* pl = reinterpret_cast<const __nv_bfloat16*>(&lo);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[pix][chunk * 8 + j] = __bfloat162float(ph[j]) + __bfloat162float(pl[j]);
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  if (w0 + tx < W) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int cl = ty + 8 * i, c = cb * 64 + cl;
+      if (c < C) y[(((int64_t)b * C + c) * H + h) * W + w0 + tx] = s[tx][cl];
+    }
+  }
+}
+
+// packed [Cout2][Cin2][taps] fp32 -> wq[(tap*2 + s)][npad][Cpt] bf16; chan_map[col] = input channel
+// of GEMM column `col` (or -1 for padding); NULL = identity.
+__global__ void cconv_prep_w_kernel(const float* __restrict__ packed, const int* __restrict__ chan_map,
+                                    __nv_bfloat16* __restrict__ wq, int Cout2, int Cin2, int taps, int npad,
+                                    int Cpt) {
+  int64_t total = (int64_t)taps * npad * Cpt;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int col = (int)(i % Cpt); int64_t r = i / Cpt;
+  int co = (int)(r % npad); int tap = (int)(r / npad);
+  int c = chan_map ? chan_map[col] : col;
+  float v = (co < Cout2 && c >= 0 && c < Cin2) ? __ldg(packed + ((int64_t)co * Cin2 + c) * taps + tap) : 0.f;
+  __nv_bfloat16 hi, lo;
+  split_bf16(v, hi, lo);
+  int64_t slab = (int64_t)npad * Cpt;
+  wq[((int64_t)tap * 2 + 0) * slab + (int64_t)co * Cpt + col] = hi;
+  wq[((int64_t)tap * 2 + 1) * slab + (int64_t)co * Cpt + col] = lo;
+}
+
+// ------------------------------------------------------------------------------ GEMM kernel
+// K-major operand tile, 128-byte swizzle: rows of 128 B (64 bf16), 8-row atoms of 1024 B back to
+// back (SBO).  (Measured on B200, scripts/mma_rate.cu: with the 64-byte swizzle every MMA costs
+// >= 140 cycles, with the 128-byte swizzle max(N/2, ~84) cycles -- so kb is always 64.)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+
+__global__ void __launch_bounds__(192, 1)
+cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t a_full[2], a_empty[2], b_full[8], b_empty[8], accum_bar;
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_ring = smem;
+  uint8_t* b_ring = smem + (size_t)p.SA * p.a_slot;
+
+  // ---- tile decode: class-major, then batch, then row tile, then column tile
+  int ci = 0;
+#pragma unroll
+  for (int c = 1; c < kMaxClasses; ++c)
+    if (c < p.ncls && (int)blockIdx.x >= p.cls[c].tile_begin) ci = c;
+  const GClass& C = p.cls[ci];
+  int t = blockIdx.x - C.tile_begin;
+  const int tw = t % C.tiles_w; t /= C.tiles_w;
+  const int th = t % C.tiles_h;
+  const int b = t / C.tiles_h;
+  const int h0 = th * p.TH * p.nacc, w0 = tw * p.TW;
+  int nacc = (C.Hq_out - h0 + p.TH - 1) / p.TH;
+  if (nacc > p.nacc) nacc = p.nacc;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmX0);
+    ptx::prefetch_tmap(&tmX1);
+    ptx::prefetch_tmap(&tmW);
+    for (int s = 0; s < p.SA; ++s) { ptx::mbar_init(&a_full[s], 1); ptx::mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < p.SB; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
+    ptx::mbar_init(&accum_bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(&tmem_base_slot, (uint32_t)p.tmem_cols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_acc = tmem_base_slot;
+  const int units = p.concat ? 1 : 2;          // B ring units per tap
+
+  if (warp == 0) {
+    if (ptx::elect_one()) {
+      // ===== TMA producer =====
+      uint32_t ia = 0, ib = 0;
+      for (int g = C.g0; g < C.g0 + C.ng; ++g) {
+        const GGroup G = p.groups[g];
+        const CUtensorMap* tm = G.src ? &tmX1 : &tmX0;
+        const int wc = p.col_mul * w0 + G.col_add, hc = p.row_mul * h0 + G.row_add;
+        for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
+          const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
+          ptx::mbar_wait(&a_empty[sa], pa ^ 1u);
+          uint8_t* as = a_ring + (size_t)sa * p.a_slot;
+          ptx::mbar_arrive_expect_tx(&a_full[sa], (uint32_t)p.a_slot);
+          ptx::tma_load_4d(as, tm, &a_full[sa], kbi * 64, wc, hc, b * 2 + 0);
+          ptx::tma_load_4d(as + p.a_half, tm, &a_full[sa], kbi * 64, wc, hc, b * 2 + 1);
+          ++ia;
+          const int kcol = p.kcol0[G.src] + kbi * 64;
+          for (int ti = 0; ti < G.ntaps; ++ti) {
+            const GTap T = p.taps[G.tap0 + ti];
+            for (int u = 0; u < units; ++u) {
+              const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
+              ptx::mbar_wait(&b_empty[sb], pb ^ 1u);
+              uint8_t* bs = b_ring + (size_t)sb * p.b_unit;
+              ptx::mbar_arrive_expect_tx(&b_full[sb], (uint32_t)p.b_unit);
+              // concat: tmW is [taps][2*npad][Cpt] (hi rows then lo rows); split: [taps*2][npad][Cpt]
+              ptx::tma_load_3d(bs, &tmW, &b_full[sb], kcol, 0, p.concat ? T.wslab : T.wslab * 2 + u);
+              ++ib;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (ptx::elect_one()) {
+      // ===== MMA issuer =====
+      const uint32_t idesc1 = ptx::make_idesc_bf16_f32(128, p.npad);
+      const uint32_t idesc2 = ptx::make_idesc_bf16_f32(128, 2 * p.npad);     // concat mode only
+      const uint32_t sub_bytes = (uint32_t)(p.TH * p.TW * 128);   // one 128-pixel sub-tile of the halo box
+      const uint32_t tw_bytes = (uint32_t)(p.TW * 128);
+      uint32_t ia = 0, ib = 0, started = 0;
+      for (int g = C.g0; g < C.g0 + C.ng; ++g) {
+        const GGroup G = p.groups[g];
+        for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
+          const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
+          ptx::mbar_wait(&a_full[sa], pa);
+          ptx::tc_fence_after();
+          const uint32_t a_base = ptx::smem_u32(a_ring + (size_t)sa * p.a_slot);
+          for (int ti = 0; ti < G.ntaps; ++ti) {
+            const GTap T = p.taps[G.tap0 + ti];
+            const uint32_t a_tap = a_base + (uint32_t)T.arow * tw_bytes;
+            for (int u = 0; u < units; ++u) {
+              const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
+              ptx::mbar_wait(&b_full[sb], pb);
+              ptx::tc_fence_after();
+              const uint64_t bd = make_desc(ptx::smem_u32(b_ring + (size_t)sb * p.b_unit));
+              for (int a = 0; a < nacc; ++a) {
+                const uint64_t a_hi = make_desc(a_tap + (uint32_t)a * sub_bytes);
+                const uint64_t a_lo = make_desc(a_tap + (uint32_t)a * sub_bytes + (uint32_t)p.a_half);
+                const uint32_t d = tmem_acc + (uint32_t)(a * p.acc_cols);
+                const uint32_t first = (started >> a) & 1u;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const uint64_t ko = (uint64_t)(k * 2);          // 16 bf16 = 32 B = 2 descriptor units
+                  if (p.concat) {
+                    // D[:, 0:2N) += a_hi * [b_hi | b_lo]   ;   D[:, 0:N) += a_lo * b_hi
+                    ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc2, first | (uint32_t)(k != 0));
+                    ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, 1);
+                  } else if (u == 0) {
+                    ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, first | (uint32_t)(k != 0));
+                    ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
+                  } else {
+                    ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
+                  }
+                }
+                started |= 1u << a;
+              }
+              ptx::umma_commit(&b_empty[sb]);
+              ++ib;
+            }
+          }
+          ptx::umma_commit(&a_empty[sa]);
+          ++ia;
+        }
+      }
+      ptx::umma_commit(&accum_bar);
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> (+bias, activation) -> NCHW fp32 and/or CL2 bf16 =====
+    const int q = warp & 3;                       // TMEM lane quarter this warp may access
+    const int m = q * 32 + lane;
+    const int hl = m / p.TW, wl = m - hl * p.TW;
+    ptx::mbar_wait(&accum_bar, 0);
+    ptx::tc_fence_after();
+    const int64_t plane = (int64_t)p.Ho * p.Wo;
+    const int cmax = p.y_cl2 != nullptr && p.y_Cp > p.npad ? p.y_Cp : p.npad;
+    const bool have = C.ng > 0;                   // a class no tap reaches is bias-only
+    for (int a = 0; a < nacc; ++a) {
+      const int qh = h0 + a * p.TH + hl, qw = w0 + wl;
+      const int ho = qh * C.oh_mul + C.oh_add, wo = qw * C.ow_mul + C.ow_add;
+      const bool ok = qh < C.Hq_out && qw < C.Wq_out && ho < p.Ho && wo < p.Wo;
+      float* yb = p.y ? p.y + (int64_t)b * p.Cout2 * plane + (int64_t)ho * p.Wo + wo : nullptr;
+      __nv_bfloat16* cb = p.y_cl2 ? p.y_cl2 + ((int64_t)b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
+      const int64_t lo_off = plane * p.y_Cp;
+      const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * p.acc_cols);
+      for (int c0 = 0; c0 < cmax; c0 += 32) {
+        uint32_t r[32], r2[32];
+        if (c0 < p.npad && have) {
+          ptx::tmem_ld_32x32(trow + (uint32_t)c0, r);
+          if (p.concat) ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
+          ptx::tmem_ld_wait();
+        }
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int co = c0 + j;
+          float f = 0.f;
+          if (co < p.Cout2 && have) {
+            f = __uint_as_float(r[j]);
+            if (p.concat) f += __uint_as_float(r2[j]);
+          }
+          if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
+          v[j] = f > 0.f ? f : f * p.slope;
+        }
+        if (!ok) continue;
+        if (yb != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c0 + j < p.Cout2) yb[(int64_t)(c0 + j) * plane] = v[j];
+        }
+        if (cb != nullptr && c0 < p.y_Cp) {
+          __align__(16) __nv_bfloat16 hi[32];
+          __align__(16) __nv_bfloat16 lo[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) split_bf16(v[j], hi[j], lo[j]);
+          uint4* dh = reinterpret_cast<uint4*>(cb + c0);
+          uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            dh[j] = reinterpret_cast<const uint4*>(hi)[j];
+            dl[j] = reinterpret_cast<const uint4*>(lo)[j];
+          }
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
+}
+
+}  // namespace se
+
+// =================================================================================== host side
+namespace se {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 tensor; dims / strides (bytes, for dims 1..rank-1) innermost-first; box = bounding box in
+// elements; estr = element (traversal) strides; zero OOB fill
+static int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                          const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr, bool sw128) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(SE_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t gdim[5], gstride[4];
+  cuuint32_t bdim[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i]; bdim[i] = box[i]; es[i] = estr[i];
+    if (i > 0) gstride[i - 1] = strides_bytes[i - 1];
+  }
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstride,
+                  bdim, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  sw128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(SE_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return SE_OK;
+}
+
+static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+static inline int pymod(int a, int b) { int r = a % b; return r < 0 ? r + b : r; }
+static inline int floordiv(int a, int b) { return (a - pymod(a, b)) / b; }
+
+// classes / groups / taps of a layer (tile-shape independent part of GemmParams)
+static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max) {
+  const bool tr = a->transposed != 0;
+  const int ph = a->ph + (tr ? 0 : a->pad_top), pw = a->pw + (tr ? 0 : a->pad_left);
+  p.ncls = 0;
+  int ng = 0, nt = 0;
+  span_max = 0;
+  const int nch = tr ? a->sh : 1, ncw = tr ? a->sw : 1;
+  p.row_mul = tr ? 1 : a->sh;
+  p.col_mul = tr ? 1 : a->sw;
+  for (int ch = 0; ch < nch; ++ch) {
+    for (int cw = 0; cw < ncw; ++cw) {
+      GClass c;
+      if (tr) {
+        c.Hq_out = (a->Ho - ch + a->sh - 1) / a->sh; c.Wq_out = (a->Wo - cw + a->sw - 1) / a->sw;
+        c.oh_mul = a->sh; c.oh_add = ch; c.ow_mul = a->sw; c.ow_add = cw;
+      } else {
+        c.Hq_out = a->Ho; c.Wq_out = a->Wo; c.oh_mul = 1; c.oh_add = 0; c.ow_mul = 1; c.ow_add = 0;
+      }
+      if (c.Hq_out <= 0 || c.Wq_out <= 0) continue;
+      c.g0 = ng; c.ng = 0;
+      const int first_group = ng;
+      // groups of source 0: one per (row phase r, kernel column dw); taps ordered by row offset
+      const int nphase = tr ? 1 : a->sh;
+      for (int r = 0; r < nphase; ++r) {
+        for (int dw = 0; dw < a->kw; ++dw) {
+          int col_add;
+          if (tr) {
+            int nw = cw + pw - dw;
+            if (pymod(nw, a->sw) != 0) continue;
+            col_add = nw / a->sw;
+          } else {
+            col_add = dw - pw;
+          }
+          int offs[kMaxTaps], slabs[kMaxTaps], n = 0;
+          for (int dh = 0; dh < a->kh; ++dh) {
+            int off;
+            if (tr) {
+              int nh = ch + ph - dh;
+              if (pymod(nh, a->sh) != 0) continue;
+              off = nh / a->sh;
+            } else {
+              if (pymod(dh - ph, a->sh) != r) continue;
+              off = floordiv(dh - ph, a->sh);
+            }
+            offs[n] = off; slabs[n] = dh * a->kw + dw; ++n;
+          }
+          if (n == 0) continue;
+          int omin = offs[0], omax = offs[0];
+          for (int i = 1; i < n; ++i) { if (offs[i] < omin) omin = offs[i]; if (offs[i] > omax) omax = offs[i]; }
+          if (ng >= kMaxGroups || nt + n > kMaxTaps) return fail(SE_ERR_UNSUPPORTED, "se_cconv_gemm: too many taps");
+          GGroup G;
+          G.row_add = (int16_t)(tr ? omin : a->sh * omin + r);
+          G.col_add = (int16_t)col_add;
+          G.src = 0; G.ntaps = (uint8_t)n; G.tap0 = (uint8_t)nt; G.pad_ = 0;
+          for (int i = 0; i < n; ++i) { p.taps[nt].arow = (uint16_t)(offs[i] - omin); p.taps[nt].wslab = (uint16_t)slabs[i]; ++nt; }
+          if (omax - omin > span_max) span_max = omax - omin;
+          p.groups[ng++] = G;
+        }
+      }
+      // source 1 re-uses the same taps
+      if (a->nsrc == 2) {
+        const int n0 = ng - first_group;
+        if (ng + n0 > kMaxGroups) return fail(SE_ERR_UNSUPPORTED, "se_cconv_gemm: too many tap groups");
+        for (int i = 0; i < n0; ++i) { GGroup G = p.groups[first_group + i]; G.src = 1; p.groups[ng++] = G; }
+      }
+      c.ng = ng - c.g0;
+      if (c.ng == 0) {
+        // a class no kernel tap reaches (kernel smaller than stride): output is bias only; keep one empty class
+      }
+      c.tiles_h = c.tiles_w = c.tile_begin = 0;
+      p.cls[p.ncls++] = c;
+    }
+  }
+  return SE_OK;
+}
+
+struct TileChoice { int TH, TW, nacc, SA, SB; double cost; };
+
+// MMA cost model measured with scripts/mma_rate.cu (cta_group::1, SS operands, 128B swizzle):
+//   cycles(128 x N x 16) = max(N / 2, ~84)
+static inline double mma_cycles(int n) { return fmax(n / 2.0, 84.0); }
+
+static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int span_max, int npad, bool concat) {
+  TileChoice best{0, 0, 0, 0, 0, 1e300};
+  const int nsm = num_sms();
+  const int acc_cols = concat ? 2 * npad : npad;
+  const int64_t b_unit = (int64_t)acc_cols * 128;                 // bytes of one B ring unit (kb = 64)
+  const int units = concat ? 1 : 2;
+  // one k-step (K = 16) of one tap on one accumulator
+  const double mma_k = concat ? mma_cycles(2 * npad) + mma_cycles(npad) : 3.0 * mma_cycles(npad);
+  for (int TW = 128; TW >= 8; TW >>= 1) {
+    const int TH = 128 / TW;
+    for (int nacc = 1; nacc <= 4; nacc <<= 1) {
+      const int tm_need = (nacc - 1) * acc_cols + (concat ? npad : 0) + round_up(npad, 32);
+      if (tm_need > 512) continue;
+      const int rows = nacc * TH + span_max;
+      if (rows * p.row_mul > 256 || TW * p.col_mul > 256) continue;
+      const int64_t a_slot = 2LL * rows * TW * 128;
+      for (int SA = 2; SA >= 1; --SA) {
+        int64_t left = kSmemBudget - 1024 - SA * a_slot;
+        if (left < 2 * b_unit) continue;
+        int SB = (int)(left / b_unit);
+        if (SB > 8) SB = 8;
+        double total = 0.0; int64_t tiles = 0;
+        for (int ci = 0; ci < p.ncls; ++ci) {
+          const GClass& c = p.cls[ci];
+          const int64_t th = (c.Hq_out + nacc * TH - 1) / (nacc * TH), tw = (c.Wq_out + TW - 1) / TW;
+          const int64_t n = th * tw * a->B;
+          const double acc_avg = (double)((c.Hq_out + TH - 1) / TH) / (double)th;   // live accumulators
+          double per_tile = 0.0;
+          for (int g = c.g0; g < c.g0 + c.ng; ++g) {
+            const GGroup& G = p.groups[g];
+            const int kblocks = (G.src ? a->src_Cp[1] : a->src_Cp[0]) / 64;
+            const double mma = G.ntaps * acc_avg * 4.0 * mma_k;
+            const double bytes = (double)a_slot + (double)G.ntaps * units * b_unit;
+            double t = fmax(mma, bytes / 36.0);
+            if (SA == 1) t += a_slot / 36.0 + 1500.0;             // single-buffered A: its load is exposed
+            per_tile += kblocks * t;
+          }
+          per_tile += 5000.0 + acc_avg * 128.0 * npad * 4.0 / 20.0;   // prologue + epilogue stores
+          total += per_tile * n;
+          tiles += n;
+        }
+        const double waves = ceil((double)tiles / nsm);
+        double cost = total / (double)tiles * waves;                 // ~cycles, 1 CTA per SM
+        if (TW < 32) cost *= 1.0 + 0.03 * (32 / TW);                 // narrow rows: poorly coalesced epilogue
+        if (cost < best.cost) best = TileChoice{TH, TW, nacc, SA, SB, cost};
+      }
+    }
+  }
+  return best;
+}
+
+int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
+  const char* nm = "se_cconv_gemm";
+  if (a->Cout2 > 256 || a->kh * a->kw > kMaxTaps)
+    return fail(SE_ERR_UNSUPPORTED, "%s: needs Cout2 <= 256 and kh*kw <= %d", nm, kMaxTaps);
+  if (a->B > 32767) return fail(SE_ERR_UNSUPPORTED, "%s: batch too large", nm);
+  if (a->transposed && (a->pad_top || a->pad_left))
+    return fail(SE_ERR_UNSUPPORTED, "%s: pad_top/pad_left only for the forward convolution", nm);
+  for (int i = 0; i < a->nsrc; ++i)
+    if (a->src_Cp[i] <= 0 || a->src_Cp[i] % 64 != 0)
+      return fail(SE_ERR_BAD_ARG, "%s: source channel pitch must be a positive multiple of 64", nm);
+
+  GemmParams p;
+  int span_max = 0;
+  int rc = build_structure(a, p, span_max);
+  if (rc != SE_OK) return rc;
+  const int npad = round_up(a->Cout2, 16);
+  static const char* force = getenv("SE_GEMM_FORCE");       // "TW,nacc,SA,concat" (tuning aid)
+  static const char* dbg_env = getenv("SE_GEMM_DEBUG");     // bit2: print the plan of every launch
+  const int dbg = dbg_env ? atoi(dbg_env) : 0;
+  bool concat = npad <= 128;
+  TileChoice tc = choose_tile(a, p, span_max, npad, concat);
+  if (force) {
+    int fTW = 0, fn = 0, fSA = 0, fc = 0;
+    if (sscanf(force, "%d,%d,%d,%d", &fTW, &fn, &fSA, &fc) == 4 && fTW >= 8 && fTW <= 128 && (fc == 0 || npad <= 128)) {
+      const int ac = fc ? 2 * npad : npad;
+      const int64_t as = 2LL * (fn * (128 / fTW) + span_max) * fTW * 128, bu = (int64_t)ac * 128;
+      int64_t left = kSmemBudget - 1024 - fSA * as;
+      int SB = left > 0 ? (int)(left / bu) : 0;
+      if (SB > 8) SB = 8;
+      if (SB >= 2 && (fn - 1) * ac + (fc ? npad : 0) + round_up(npad, 32) <= 512) {
+        concat = fc != 0;
+        tc = TileChoice{128 / fTW, fTW, fn, fSA, SB, 0.0};
+      }
+    }
+  }
+  if (tc.TW == 0) return fail(SE_ERR_UNSUPPORTED, "%s: no tile shape fits shared memory", nm);
+  p.TH = tc.TH; p.TW = tc.TW; p.nacc = tc.nacc;
+  p.concat = concat ? 1 : 0; p.acc_cols = concat ? 2 * npad : npad;
+  const int rows = tc.nacc * tc.TH + span_max;
+  p.a_half = rows * tc.TW * 128; p.a_slot = 2 * p.a_half;
+  p.b_unit = p.acc_cols * 128;
+  p.SA = tc.SA; p.SB = tc.SB;
+  p.Ho = a->Ho; p.Wo = a->Wo; p.Cout2 = a->Cout2; p.npad = npad; p.y_Cp = a->y_Cp;
+  const int tm_need = (tc.nacc - 1) * p.acc_cols + (concat ? npad : 0) + round_up(npad, 32);
+  p.tmem_cols = 32; while (p.tmem_cols < tm_need) p.tmem_cols <<= 1;
+  p.bias = a->bias; p.slope = a->slope; p.y = a->y_nchw; p.y_cl2 = reinterpret_cast<__nv_bfloat16*>(a->y_cl2);
+  p.kblocks[0] = a->src_Cp[0] / 64; p.kcol0[0] = 0;
+  p.kblocks[1] = a->nsrc == 2 ? a->src_Cp[1] / 64 : 0; p.kcol0[1] = a->src_Cp[0];
+  int64_t ntiles = 0;
+  for (int ci = 0; ci < p.ncls; ++ci) {
+    GClass& c = p.cls[ci];
+    c.tiles_h = (c.Hq_out + tc.nacc * tc.TH - 1) / (tc.nacc * tc.TH);
+    c.tiles_w = (c.Wq_out + tc.TW - 1) / tc.TW;
+    c.tile_begin = (int)ntiles;
+    ntiles += (int64_t)c.tiles_h * c.tiles_w * a->B;
+  }
+  if (ntiles <= 0) return SE_OK;
+  if (ntiles > 2147483647LL) return fail(SE_ERR_UNSUPPORTED, "%s: too many tiles", nm);
+
+  CUtensorMap tmX[2], tmW;
+  for (int i = 0; i < 2; ++i) {
+    const int j = i < a->nsrc ? i : 0;
+    const uint64_t Cp = (uint64_t)a->src_Cp[j];
+    uint64_t dims[4] = {Cp, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)(a->B * 2)};
+    uint64_t str[3] = {Cp * 2, (uint64_t)a->src_Wpitch[j] * Cp * 2,
+                       (uint64_t)a->src_Hpitch[j] * a->src_Wpitch[j] * Cp * 2};
+    uint32_t box[4] = {64, (uint32_t)(tc.TW * p.col_mul), (uint32_t)(rows * p.row_mul), 1};
+    uint32_t es[4] = {1, (uint32_t)p.col_mul, (uint32_t)p.row_mul, 1};
+    rc = make_tmap_bf16(&tmX[i], a->src[j], 4, dims, str, box, es, true);
+    if (rc != SE_OK) return rc;
+  }
+  {
+    // wq is [taps][2][npad][Cpt]; concat views it as [taps][2*npad][Cpt], split as [taps*2][npad][Cpt]
+    const uint64_t Cpt = (uint64_t)a->src_Cp[0] + (a->nsrc == 2 ? a->src_Cp[1] : 0);
+    const uint64_t rows_u = (uint64_t)p.acc_cols, nu = (uint64_t)a->kh * a->kw * (concat ? 1 : 2);
+    uint64_t dims[3] = {Cpt, rows_u, nu};
+    uint64_t str[2] = {Cpt * 2, Cpt * 2 * rows_u};
+    uint32_t box[3] = {64, (uint32_t)rows_u, 1};
+    uint32_t es[3] = {1, 1, 1};
+    rc = make_tmap_bf16(&tmW, a->wq, 3, dims, str, box, es, true);
+    if (rc != SE_OK) return rc;
+  }
+  const int smem = p.SA * p.a_slot + p.SB * p.b_unit + 1024;
+  static int smem_attr = 0;
+  if (smem > smem_attr) {
+    SE_CUDA(cudaFuncSetAttribute(cconv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    smem_attr = smem;
+  }
+  if (dbg & 4)
+    fprintf(stderr, "se_cconv_gemm: tr=%d Cp=%d+%d N=%d k=%dx%d s=%dx%d -> TH=%d TW=%d nacc=%d concat=%d SA=%d SB=%d rows=%d smem=%d tmem=%d tiles=%lld ncls=%d\n",
+            a->transposed, a->src_Cp[0], a->nsrc == 2 ? a->src_Cp[1] : 0, npad, a->kh, a->kw, a->sh, a->sw, tc.TH, tc.TW,
+            tc.nacc, p.concat, tc.SA, tc.SB, rows, smem, p.tmem_cols, (long long)ntiles, p.ncls);
+  cconv_gemm_kernel<<<(unsigned)ntiles, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
+  return check_launch("cconv_gemm_kernel");
+}
+
+}  // namespace se
+
+// ---- nn.Module path: NCHW fp32 in / out through a caller-provided workspace -------------------
+namespace se {
+
+static void module_plan(int64_t B, int Cin2, int H, int W, int Cout2, int taps, int& Cp, int64_t& xs_bytes,
+                        int64_t& wq_bytes) {
+  Cp = round_up(Cin2, 64);
+  xs_bytes = (B * 2 * (int64_t)H * W * Cp * 2 + 1023) / 1024 * 1024;
+  wq_bytes = ((int64_t)taps * 2 * round_up(Cout2, 16) * Cp * 2 + 1023) / 1024 * 1024;
+}
+
+bool cconv_umma_supported(bool transposed, int64_t B, const ConvGeom& g) {
+  (void)transposed;
+  return g.Cout2 <= 256 && g.kh * g.kw <= kMaxTaps && B <= 32767 && g.Cin2 >= 16;
+}
+
+int64_t cconv_umma_workspace_bytes(bool transposed, int64_t B, int Cin2, int H, int W, int Cout2, int kh,
+                                   int kw, int sh, int sw) {
+  (void)transposed; (void)sh; (void)sw;
+  int Cp; int64_t xs, wq;
+  module_plan(B, Cin2, H, W, Cout2, kh * kw, Cp, xs, wq);
+  return xs + wq + 1024;
+}
+
+int cconv_fwd_umma(bool transposed, const float* x, const float* packed, const float* bias, int64_t B,
+                   const ConvGeom& g, float* y, void* ws, int64_t ws_bytes, cudaStream_t s) {
+  int Cp; int64_t xs_bytes, wq_bytes;
+  module_plan(B, g.Cin2, g.H, g.W, g.Cout2, g.kh * g.kw, Cp, xs_bytes, wq_bytes);
+  uintptr_t base = (reinterpret_cast<uintptr_t>(ws) + 1023) & ~uintptr_t(1023);
+  if (ws == nullptr || (int64_t)(base - reinterpret_cast<uintptr_t>(ws)) + xs_bytes + wq_bytes > ws_bytes)
+    return fail(SE_ERR_WORKSPACE, "se_cconv*_fwd: workspace of %lld bytes needed (se_cconv_workspace_bytes)",
+                (long long)(xs_bytes + wq_bytes + 1024));
+  void* xs = reinterpret_cast<void*>(base);
+  void* wq = reinterpret_cast<void*>(base + xs_bytes);
+  int rc = se_cl2_from_nchw(x, B, g.Cin2, g.H, g.W, xs, Cp, s);
+  if (rc != SE_OK) return rc;
+  rc = se_cconv_prep_weight(packed, g.Cout2, g.Cin2, g.kh * g.kw, nullptr, Cp, wq, s);
+  if (rc != SE_OK) return rc;
+  se_cconv_args a{};
+  a.transposed = transposed ? 1 : 0; a.B = B; a.nsrc = 1;
+  a.src[0] = xs; a.src_Cp[0] = Cp; a.H = g.H; a.W = g.W; a.src_Hpitch[0] = g.H; a.src_Wpitch[0] = g.W;
+  a.Cout2 = g.Cout2; a.kh = g.kh; a.kw = g.kw; a.sh = g.sh; a.sw = g.sw; a.ph = g.ph; a.pw = g.pw;
+  a.Ho = g.Ho; a.Wo = g.Wo; a.wq = wq; a.bias = bias; a.slope = 1.f; a.y_nchw = y;
+  return se_cconv_gemm(&a, s);
+}
+
+}  // namespace se
+
+// =================================================================================== C ABI
+extern "C" int se_cconv_gemm(const se_cconv_args* a, void* stream) {
+  SE_REQUIRE(a != nullptr, "se_cconv_gemm: null args");
+  SE_REQUIRE(a->nsrc == 1 || a->nsrc == 2, "se_cconv_gemm: nsrc must be 1 or 2");
+  SE_REQUIRE(a->src[0] && (a->nsrc == 1 || a->src[1]) && a->wq, "se_cconv_gemm: null pointer");
+  SE_REQUIRE(a->y_nchw || a->y_cl2, "se_cconv_gemm: no output requested");
+  SE_REQUIRE(a->B >= 0 && a->H > 0 && a->W > 0 && a->Cout2 > 0 && a->kh > 0 && a->kw > 0 && a->sh > 0 &&
+             a->sw > 0 && a->Ho > 0 && a->Wo > 0, "se_cconv_gemm: bad geometry");
+  SE_REQUIRE(a->y_cl2 == nullptr || (a->y_Cp >= a->Cout2 && a->y_Cp % 64 == 0),
+             "se_cconv_gemm: y_Cp must be a multiple of 64 >= Cout2");
+  for (int i = 0; i < a->nsrc; ++i)
+    SE_REQUIRE(a->src_Hpitch[i] >= a->H && a->src_Wpitch[i] >= a->W, "se_cconv_gemm: source pitch < extent");
+  if (a->B == 0) return SE_OK;
+  return se::cconv_gemm_launch(a, (cudaStream_t)stream);
+}
+
+extern "C" int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream) {
+  SE_REQUIRE(x && cl2, "se_cl2_from_nchw: null pointer");
+  SE_REQUIRE(B >= 0 && C > 0 && H > 0 && W > 0 && Cp >= C && Cp % 64 == 0, "se_cl2_from_nchw: bad dims");
+  if (B == 0) return SE_OK;
+  dim3 grid((unsigned)((W + 31) / 32), (unsigned)H, (unsigned)(B * (Cp / 64)));
+  if (grid.y > 65535 || grid.z > 65535) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_nchw: tensor too large");
+  se::cl2_from_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<__nv_bfloat16*>(cl2), C, H, W, Cp);
+  return se::check_launch("se_cl2_from_nchw");
+}
+
+extern "C" int se_cl2_to_nchw(const void* cl2, int64_t B, int C, int H, int W, int Cp, float* y, void* stream) {
+  SE_REQUIRE(y && cl2, "se_cl2_to_nchw: null pointer");
+  SE_REQUIRE(B >= 0 && C > 0 && H > 0 && W > 0 && Cp >= C && Cp % 64 == 0, "se_cl2_to_nchw: bad dims");
+  if (B == 0) return SE_OK;
+  dim3 grid((unsigned)((W + 31) / 32), (unsigned)H, (unsigned)(B * (Cp / 64)));
+  if (grid.y > 65535 || grid.z > 65535) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_to_nchw: tensor too large");
+  se::cl2_to_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const __nv_bfloat16*>(cl2), y, C, H, W, Cp);
+  return se::check_launch("se_cl2_to_nchw");
+}
+
+extern "C" int64_t se_cconv_wq_elems(int Cout2, int Cp_total, int taps) {
+  return (int64_t)taps * 2 * ((Cout2 + 15) / 16 * 16) * Cp_total;
+}
+
+extern "C" int se_cconv_prep_weight(const float* packed, int Cout2, int Cin2, int taps, const int* chan_map,
+                                    int Cp_total, void* wq, void* stream) {
+  SE_REQUIRE(packed && wq, "se_cconv_prep_weight: null pointer");
+  SE_REQUIRE(Cout2 > 0 && Cin2 > 0 && taps > 0 && Cp_total > 0 && Cp_total % 64 == 0,
+             "se_cconv_prep_weight: bad dims");
+  const int npad = (Cout2 + 15) / 16 * 16;
+  int64_t total = (int64_t)taps * npad * Cp_total;
+  se::cconv_prep_w_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      packed, chan_map, reinterpret_cast<__nv_bfloat16*>(wq), Cout2, Cin2, taps, npad, Cp_total);
+  return se::check_launch("se_cconv_prep_weight");
+}

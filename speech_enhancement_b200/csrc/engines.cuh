@@ -26,4 +26,8 @@ int64_t cconv_umma_workspace_bytes(bool transposed, int64_t B, int Cin2, int H, 
 int cconv_fwd_umma(bool transposed, const float* x, const float* packed, const float* bias,
                    int64_t B, const ConvGeom& g, float* y, void* ws, int64_t ws_bytes, cudaStream_t s);
 
+// cconv_direct.cu (HBM-bound degenerate layers, exact fp32)
+int cconv_fwd_small_cout(bool transposed, const float* x, const float* packed, const float* bias, int64_t B,
+                         const ConvGeom& g, float* y, cudaStream_t s);
+
 }  // namespace se

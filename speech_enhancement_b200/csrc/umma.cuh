@@ -118,6 +118,26 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// variants with operand-collector hints (the tensor core keeps A, or in .ws mode B, in its collector
+// buffer so the next MMA does not re-read it from shared memory)
+#define SE_UMMA_VARIANT(NAME, OPCODE)                                                                   \
+  __device__ __forceinline__ void NAME(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, \
+                                       uint32_t accumulate) {                                           \
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t" OPCODE " [%0], %1, %2, %3, p;\n\t}"    \
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");      \
+  }
+SE_UMMA_VARIANT(umma_bf16_a_fill, "tcgen05.mma.cta_group::1.kind::f16.collector::a::fill")
+SE_UMMA_VARIANT(umma_bf16_a_use, "tcgen05.mma.cta_group::1.kind::f16.collector::a::use")
+SE_UMMA_VARIANT(umma_bf16_a_lastuse, "tcgen05.mma.cta_group::1.kind::f16.collector::a::lastuse")
+SE_UMMA_VARIANT(umma_ws_bf16, "tcgen05.mma.ws.cta_group::1.kind::f16")
+SE_UMMA_VARIANT(umma_ws_bf16_b0_fill, "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::fill")
+SE_UMMA_VARIANT(umma_ws_bf16_b0_use, "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::use")
+SE_UMMA_VARIANT(umma_ws_bf16_b0_lastuse, "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b0::lastuse")
+SE_UMMA_VARIANT(umma_ws_bf16_b1_fill, "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b1::fill")
+SE_UMMA_VARIANT(umma_ws_bf16_b1_use, "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b1::use")
+SE_UMMA_VARIANT(umma_ws_bf16_b1_lastuse, "tcgen05.mma.ws.cta_group::1.kind::f16.collector::b1::lastuse")
+#undef SE_UMMA_VARIANT
+
 // mbarrier arrives once every previously issued tcgen05.mma of this thread has completed
 // (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
