@@ -149,42 +149,27 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------------------ GPU arm
 class StageTimer:
-    """CUDA-event timing of the hot-path stages via module/function hooks (used in a SEPARATE
-    profiling pass after the headline timing, so the hooks never perturb `value`)."""
+    """CUDA-event timing of the hot-path stages through the package's `_abi.stage` brackets (used in a
+    SEPARATE profiling pass after the headline timing, so it never perturbs `value`)."""
 
-    def __init__(self, model):
-        import speech_enhancement_b200 as se
-        self.events = {'stft': [], 'istft': [], 'cconv': [], 'mask': []}
-        self.handles = []
-        for m in model.modules():
-            kind = ('stft' if isinstance(m, se.ConvSTFT) else 'istft' if isinstance(m, se.ConviSTFT)
-                    else 'cconv' if isinstance(m, (se.ComplexConv2d, se.ComplexConvTranspose2d)) else None)
-            if kind:
-                self.handles.append(m.register_forward_pre_hook(lambda mod, inp, k=kind: self._start(k)))
-                self.handles.append(m.register_forward_hook(lambda mod, inp, out, k=kind: self._stop(k)))
-        ops, self._ops, self._orig = model._ops, model._ops, model._ops.mask_dccrn
+    def __init__(self):
+        from speech_enhancement_b200 import _abi
+        self._abi = _abi
+        self.events = {}
+        _abi._timer = self
 
-        def timed_mask(*a, **kw):
-            self._start('mask')
-            r = self._orig(*a, **kw)
-            self._stop('mask')
-            return r
-        ops.mask_dccrn = timed_mask
-
-    def _start(self, k):
+    def start(self, k):
         e = torch.cuda.Event(enable_timing=True)
         e.record()
-        self.events[k].append([e, None])
+        self.events.setdefault(k, []).append([e, None])
 
-    def _stop(self, k):
+    def stop(self, k):
         e = torch.cuda.Event(enable_timing=True)
         e.record()
         self.events[k][-1][1] = e
 
     def close(self):
-        for h in self.handles:
-            h.remove()
-        self._ops.mask_dccrn = self._orig
+        self._abi._timer = None
 
     def totals_ms(self):
         torch.cuda.synchronize()
@@ -273,12 +258,14 @@ def run_ours(args):
 
     # ---- per-stage profiling pass (rank 0 only, hooks + events; not part of `value`) ----
     pk = peaks()
-    st = StageTimer(model)
+    st = StageTimer()
     nprof = min(args.steps, 5)
     for i in range(nprof):
         step(i)
     tot = st.totals_ms()
     st.close()
+    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2'):
+        tot.setdefault(k, 0.0)
     T = (L + 512 - 400) // 100 + 1
     Lp = out_len or (T - 1) * 100 + 400 - 512
     alg = {'stft': 4 * (L + 514 * T), 'istft': 4 * (514 * T + Lp), 'mask': 4 * 6 * 257 * T}
@@ -289,7 +276,8 @@ def run_ours(args):
         stages[k] = {'ms': t * 1e3, 'GB/s': gbs, 'frac_hbm': gbs / pk['hbm_gbs']}
     t_conv = tot['cconv'] / nprof / 1e3
     tflops = CONV_GFLOP_PER_UTT * B / t_conv / 1e3
-    stages['cconv'] = {'ms': t_conv * 1e3, 'TFLOP/s': tflops, 'launches': len(st.events['cconv']) // nprof}
+    stages['cconv'] = {'ms': t_conv * 1e3, 'TFLOP/s': tflops, 'launches': len(st.events.get('cconv', [])) // nprof}
+    stages['cl2_convert_ms'] = tot['cl2'] / nprof
     stages['step_ms'] = ms / args.steps
     stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / args.steps)
     roofline = {'bound': 'tensor', 'kernel': 'complex conv stack (12 se_cconv*_fwd launches per step)',

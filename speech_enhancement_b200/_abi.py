@@ -92,6 +92,28 @@ def check(rc):
         raise _EXC.get(rc, RuntimeError)(f'libse_b200: {msg} (code {rc})')
 
 
+# ---- optional per-stage timing (bench.py installs a timer; no-op otherwise) ----------------------
+_timer = None
+
+
+class stage:
+    """`with _abi.stage('cconv'):` brackets the launches of one hot-path stage for bench.py's CUDA-event
+    profiling pass; costs one attribute test when no timer is installed."""
+    __slots__ = ('kind',)
+
+    def __init__(self, kind):
+        self.kind = kind
+
+    def __enter__(self):
+        if _timer is not None:
+            _timer.start(self.kind)
+
+    def __exit__(self, *exc):
+        if _timer is not None:
+            _timer.stop(self.kind)
+        return False
+
+
 def stream_ptr():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 

@@ -110,8 +110,65 @@ class DCCRN(nn.Module):
         freq = fft_size // 2 // (2 ** len(enc)) * enc[-1]
         self.lstm = _LSTMBlock(freq, lstm_channels, linear_channels, num_layers=2, batch_first=True,
                                bidirectional=bidirectional)
+        self._fb = None
+
+    # eval-mode / no-grad forwards on CUDA run the chained engine (chain.py): BN, activation, causal
+    # pad and skip concat are folded into the conv kernels and activations stay in CL2 between layers
+    fused = True
+
+    def _use_fused(self, x):
+        return (self.fused and not self.training and not torch.is_grad_enabled() and x.is_cuda
+                and hasattr(self.encoder.layers[0], 'conv')
+                and type(self.encoder.layers[0].conv).__module__.startswith('speech_enhancement_b200'))
+
+    def _fused_blocks(self):
+        if self._fb is None:
+            from .chain import FusedBlock
+            enc = [FusedBlock(l.conv, l.norm, l.act) for l in self.encoder.layers]
+            dec = []
+            for l in self.decoder.layers:
+                cin2 = 2 * l.conv_transposed.real_conv.weight.shape[0]
+                dec.append(FusedBlock(l.conv_transposed, l.norm, l.act, src_channels=[cin2 // 2, cin2 // 2],
+                                      concat='complex'))
+            self._fb = (enc, dec)
+        return self._fb
+
+    def _forward_fused(self, x):
+        from .chain import cl2_from_nchw
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)                                               # [B, 2F, T] fp32
+        B, C2, T = spec.shape
+        noisy_real, noisy_imag = _spec_planes(spec, n_bins)
+        enc, dec = self._fused_blocks()
+        # enc0 reads the real / imag row blocks of `spec` in place (DC bin skipped, causal frame pad)
+        act, _ = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1)
+        skips = [act]
+        nchw = None
+        for i in range(1, len(enc)):
+            last = i == len(enc) - 1
+            act, nchw = enc[i]([act], pad_left=1, out_cl2=True, out_nchw=last)
+            skips.append(act)
+        b, c, f, t = nchw.shape
+        h = self.lstm(nchw.reshape(b, c * f, t).permute(0, 2, 1))
+        act = cl2_from_nchw(h.permute(0, 2, 1).reshape(b, c, f, t))
+        y = None
+        for i, blk in enumerate(dec):
+            skip = skips.pop()
+            if act.W > skip.W:
+                act = act.trimmed(W=skip.W)
+            last = i == len(dec) - 1
+            act, y = blk([act, skip], out_cl2=not last, out_nchw=last)
+        y = F.pad(y, (0, 0, 1, 0))                                        # zero DC row (:169)
+        mask_real, mask_imag = y[:, 0], y[:, 1]
+        if mask_real.shape[-1] > noisy_real.shape[-1]:
+            mask_real, mask_imag = mask_real[..., :-1], mask_imag[..., :-1]
+        est_spec = self._ops.mask_dccrn(self.masking, noisy_real, noisy_imag, mask_real, mask_imag)
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp_(wav, -1, 1)
 
     def forward(self, x):
+        if self._use_fused(x):
+            return self._forward_fused(x)
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)                                               # [B, 2F, T]
         noisy_real, noisy_imag = _spec_planes(spec, n_bins)

@@ -1,0 +1,241 @@
+"""Layer chaining on the tcgen05 conv engine: activations stay in CL2 between layers.
+
+The reference runs every encoder / decoder block as  F.pad -> ComplexConv -> ComplexBatchNorm2d ->
+activation  with a `complex_concat` / `torch.cat` of the skip in front of every decoder block
+(_2008_00264_dccrn.py:27-33, :51-57, :113-121; _1903_03107_dcunet.py:84-95; _2206_07293_frcrn.py:90-102).
+In eval mode all of that is linear glue around the convolution, so a `FusedBlock` folds it into the
+conv kernel's operands and epilogue:
+
+  * complex BN with running statistics is a per-channel 2x2 affine  y = Z (x - M) + B
+    (complex_nn.py:252-322): Z is folded into the packed weight rows, Z(b - M) + B into the bias;
+  * PReLU / LeakyReLU / ReLU are the epilogue's  v > 0 ? v : slope * v;
+  * the causal frame pad is a coordinate shift with TMA zero fill (`pad_left`);
+  * the skip concat is a second K range read from the skip's own CL2 tensor (`chan_map` permutes the
+    weight columns at pack time), the T-trim before it is the tensor map's extent.
+
+Everything here is host-side orchestration; the arithmetic is in libse_b200.so (se_cconv_gemm,
+se_cconv_small_cin, se_cl2_from_nchw, se_cl2_to_nchw).
+"""
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _abi
+
+
+def _cp(c):
+    return (c + 63) // 64 * 64
+
+
+class Act:
+    """A CL2 activation: bf16 [B, 2, Hp, Wp, Cp] (value = hi + lo) with logical extent C x H x W."""
+    __slots__ = ('data', 'C', 'H', 'W')
+
+    def __init__(self, data, C_, H, W):
+        self.data, self.C, self.H, self.W = data, C_, H, W
+
+    @property
+    def B(self):
+        return self.data.shape[0]
+
+    @property
+    def Cp(self):
+        return self.data.shape[4]
+
+    def trimmed(self, H=None, W=None):
+        """same storage, smaller logical extent (the reference's x[..., :-1] before a decoder block)"""
+        return Act(self.data, self.C, self.H if H is None else H, self.W if W is None else W)
+
+
+def cl2_empty(B, C_, H, W, device):
+    return Act(torch.empty((B, 2, H, W, _cp(C_)), device=device, dtype=torch.bfloat16), C_, H, W)
+
+
+def cl2_from_nchw(x):
+    x = _abi.require_cuda_f32(x, 'cl2_from_nchw(x)').contiguous()
+    B, C_, H, W = x.shape
+    out = cl2_empty(B, C_, H, W, x.device)
+    with torch.cuda.device(x.device), _abi.stage('cl2'):
+        _abi.check(_abi.lib().se_cl2_from_nchw(_abi.ptr(x), B, C_, H, W, _abi.ptr(out.data), out.Cp,
+                                               _abi.stream_ptr()))
+    return out
+
+
+def cl2_to_nchw(act):
+    d = act.data
+    if d.shape[2] != act.H or d.shape[3] != act.W:
+        raise RuntimeError('cl2_to_nchw: trimmed views are not supported')
+    y = torch.empty((act.B, act.C, act.H, act.W), device=d.device, dtype=torch.float32)
+    with torch.cuda.device(d.device):
+        _abi.check(_abi.lib().se_cl2_to_nchw(_abi.ptr(d), act.B, act.C, act.H, act.W, act.Cp, _abi.ptr(y),
+                                             _abi.stream_ptr()))
+    return y
+
+
+def _pair(v):
+    return (v, v) if isinstance(v, int) else tuple(v)
+
+
+def _slope_of(act):
+    if act is None or isinstance(act, nn.Identity):
+        return 1.0, ()
+    if isinstance(act, nn.PReLU):
+        if act.weight.numel() != 1:
+            raise RuntimeError('FusedBlock: per-channel PReLU is not supported')
+        return None, (act.weight,)
+    if isinstance(act, nn.LeakyReLU):
+        return float(act.negative_slope), ()
+    if isinstance(act, nn.ReLU):
+        return 0.0, ()
+    raise RuntimeError(f'FusedBlock: unsupported activation {type(act).__name__}')
+
+
+def concat_channel_map(src_channels, mode):
+    """module input channel behind every GEMM column, sources laid out back to back (each padded to 64).
+
+    mode 'complex': the module sees complex_concat(sources) = [all real halves | all imaginary halves]
+    (complex_nn.py:4-16); mode 'plain': torch.cat(sources, 1) (_1903_03107_dcunet.py:93)."""
+    maps = []
+    if mode == 'complex':
+        half_total = sum(c // 2 for c in src_channels)
+        off = 0
+        for c in src_channels:
+            h = c // 2
+            m = [off + j for j in range(h)] + [half_total + off + j for j in range(h)]
+            maps.append(m + [-1] * (_cp(c) - c))
+            off += h
+    elif mode == 'plain':
+        off = 0
+        for c in src_channels:
+            maps.append(list(range(off, off + c)) + [-1] * (_cp(c) - c))
+            off += c
+    else:
+        raise ValueError(mode)
+    return [v for m in maps for v in m]
+
+
+class FusedBlock:
+    """conv / convT (+ eval-mode complex BN) (+ leaky activation) of one reference block, prepared for
+    the chained engine.  `conv` is a ComplexConv2d / ComplexConvTranspose2d of this package."""
+
+    def __init__(self, conv, norm=None, act=None, src_channels=None, concat='complex'):
+        self.conv, self.norm, self.act = conv, norm, act
+        rc = conv.real_conv
+        self.transposed = bool(conv._transposed)
+        if self.transposed:
+            ci, co = rc.weight.shape[0], rc.weight.shape[1]
+        else:
+            co, ci = rc.weight.shape[0], rc.weight.shape[1]
+        self.cin2, self.cout2 = 2 * ci, 2 * co
+        self.kh, self.kw = rc.weight.shape[2], rc.weight.shape[3]
+        self.sh, self.sw = _pair(rc.stride)
+        self.ph, self.pw = _pair(rc.padding)
+        self.oph, self.opw = _pair(rc.output_padding) if self.transposed else (0, 0)
+        self.src_channels = list(src_channels) if src_channels is not None else [self.cin2]
+        if sum(self.src_channels) != self.cin2:
+            raise RuntimeError(f'FusedBlock: sources {self.src_channels} do not add up to {self.cin2} channels')
+        self.concat = concat
+        self._key = None
+        self._ops = None
+
+    # ---- folded operands, rebuilt when any parameter / buffer changes
+    def _operands(self):
+        conv, norm = self.conv, self.norm
+        slope_const, slope_t = _slope_of(self.act)
+        ts = [conv.real_conv.weight, conv.imag_conv.weight]
+        if conv.real_conv.bias is not None:
+            ts += [conv.real_conv.bias, conv.imag_conv.bias]
+        has_bn = norm is not None and not isinstance(norm, nn.Identity)
+        if has_bn:
+            if norm.training or not norm.track_running_stats:
+                raise RuntimeError('FusedBlock: complex BN can only be folded in eval mode with running stats')
+            ts += [norm.RMr, norm.RMi, norm.RVrr, norm.RVri, norm.RVii]
+            if norm.affine:
+                ts += [norm.Wrr, norm.Wri, norm.Wii, norm.Br, norm.Bi]
+        ts += list(slope_t)
+        key = tuple((t.data_ptr(), t._version) for t in ts)
+        if key == self._key:
+            return self._ops
+        with torch.no_grad():
+            packed, bias, co, ci, kh, kw = conv._packed()           # fp32 [2co, 2ci*kh*kw], [2co] | None
+            dev = packed.device
+            if bias is None:
+                bias = torch.zeros(2 * co, device=dev, dtype=torch.float32)
+            if has_bn:
+                Zrr, Zri, Zir, Zii = norm._affine_2x2(norm.RVrr, norm.RVri, norm.RVii)
+                Wr, Wi = packed[:co], packed[co:]
+                br, bi = bias[:co] - norm.RMr, bias[co:] - norm.RMi
+                packed = torch.cat([Zrr[:, None] * Wr + Zri[:, None] * Wi, Zir[:, None] * Wr + Zii[:, None] * Wi], 0)
+                nbr, nbi = Zrr * br + Zri * bi, Zir * br + Zii * bi
+                if norm.affine:
+                    nbr, nbi = nbr + norm.Br, nbi + norm.Bi
+                bias = torch.cat([nbr, nbi])
+            packed = packed.contiguous().float()
+            bias = bias.contiguous().float()
+            slope = slope_const if slope_const is not None else float(slope_t[0].detach().float().item())
+            cmap = concat_channel_map(self.src_channels, self.concat)
+            cpt = len(cmap)
+            cmap_t = torch.tensor(cmap, device=dev, dtype=torch.int32)
+            lib = _abi.lib()
+            taps = kh * kw
+            wq = torch.empty((lib.se_cconv_wq_elems(2 * co, cpt, taps),), device=dev, dtype=torch.bfloat16)
+            with torch.cuda.device(dev):
+                _abi.check(lib.se_cconv_prep_weight(_abi.ptr(packed), 2 * co, 2 * ci, taps, _abi.ptr(cmap_t), cpt,
+                                                    _abi.ptr(wq), _abi.stream_ptr()))
+        self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt}
+        self._key = key
+        return self._ops
+
+    def out_size(self, H, W, pad_top=0, pad_left=0):
+        if self.transposed:
+            return ((H - 1) * self.sh - 2 * self.ph + self.kh + self.oph,
+                    (W - 1) * self.sw - 2 * self.pw + self.kw + self.opw)
+        return ((H + pad_top + 2 * self.ph - self.kh) // self.sh + 1,
+                (W + pad_left + 2 * self.pw - self.kw) // self.sw + 1)
+
+    def __call__(self, srcs, pad_top=0, pad_left=0, out_cl2=True, out_nchw=False):
+        """srcs: list of Act with the same logical H, W.  Returns (Act | None, NCHW fp32 tensor | None)."""
+        ops = self._operands()
+        if len(srcs) != len(self.src_channels) or any(s.C != c for s, c in zip(srcs, self.src_channels)):
+            raise RuntimeError(f'FusedBlock: expected sources with channels {self.src_channels}')
+        H, W, B = srcs[0].H, srcs[0].W, srcs[0].B
+        if any(s.H != H or s.W != W or s.B != B for s in srcs):
+            raise RuntimeError('FusedBlock: sources disagree on their logical extent')
+        Ho, Wo = self.out_size(H, W, pad_top, pad_left)
+        dev = srcs[0].data.device
+        y_act = cl2_empty(B, self.cout2, Ho, Wo, dev) if out_cl2 else None
+        y = torch.empty((B, self.cout2, Ho, Wo), device=dev, dtype=torch.float32) if out_nchw else None
+        a = _abi.ConvArgs()
+        a.transposed, a.B, a.nsrc = int(self.transposed), B, len(srcs)
+        for i, s in enumerate(srcs):
+            a.src[i] = s.data.data_ptr()
+            a.src_Cp[i], a.src_Hpitch[i], a.src_Wpitch[i] = s.Cp, s.data.shape[2], s.data.shape[3]
+        a.H, a.W, a.pad_top, a.pad_left = H, W, pad_top, pad_left
+        a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw, a.Ho, a.Wo = (self.cout2, self.kh, self.kw, self.sh,
+                                                                    self.sw, self.ph, self.pw, Ho, Wo)
+        a.wq, a.bias, a.slope = ops['wq'].data_ptr(), ops['bias'].data_ptr(), ops['slope']
+        a.y_nchw = y.data_ptr() if y is not None else None
+        a.y_cl2 = y_act.data.data_ptr() if y_act is not None else None
+        a.y_Cp = y_act.Cp if y_act is not None else 0
+        with torch.cuda.device(dev), _abi.stage('cconv'):
+            _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+        return y_act, y
+
+    def first_layer(self, x, xs_b, xs_c, xs_h, B, H, W, pad_top=0, pad_left=0, out_cl2=True, out_nchw=False):
+        """the 2-input-channel first encoder layer, reading fp32 planes in place through strides
+        (`x` is any tensor whose data_ptr is the first element of channel 0)."""
+        if self.transposed:
+            raise RuntimeError('FusedBlock.first_layer: forward convolution only')
+        ops = self._operands()
+        Ho, Wo = self.out_size(H, W, pad_top, pad_left)
+        dev = x.device
+        y_act = cl2_empty(B, self.cout2, Ho, Wo, dev) if out_cl2 else None
+        y = torch.empty((B, self.cout2, Ho, Wo), device=dev, dtype=torch.float32) if out_nchw else None
+        with torch.cuda.device(dev), _abi.stage('cconv'):
+            _abi.check(_abi.lib().se_cconv_small_cin(
+                _abi.ptr(x), xs_b, xs_c, xs_h, B, self.cin2, H, W, pad_top, pad_left, _abi.ptr(ops['packed']),
+                _abi.ptr(ops['bias']), ops['slope'], self.cout2, self.kh, self.kw, self.sh, self.sw, self.ph,
+                self.pw, _abi.ptr(y), _abi.ptr(y_act.data) if y_act is not None else None,
+                y_act.Cp if y_act is not None else 0, Ho, Wo, _abi.stream_ptr()))
+        return y_act, y

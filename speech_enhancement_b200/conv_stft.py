@@ -72,7 +72,7 @@ class ConvSTFT(nn.Module):
             raise RuntimeError(f'ConvSTFT: input length {L} is shorter than one window ({win})')
         T = (L + 2 * pad - win) // self.hop_size + 1
         out = torch.empty((B, c2, T), device=x.device, dtype=torch.float32)
-        with torch.cuda.device(x.device):
+        with torch.cuda.device(x.device), _abi.stage('stft'):
             _abi.check(_abi.lib().se_stft_fwd(_abi.ptr(x), B, L, _abi.ptr(w), c2, win, self.hop_size,
                                               self.pad, int(self.center), _abi.ptr(out), T,
                                               _abi.stream_ptr()))
@@ -144,7 +144,7 @@ class ConviSTFT(nn.Module):
         out = torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
         if out_len == 0 or B == 0:
             return out
-        with torch.cuda.device(spec.device):
+        with torch.cuda.device(spec.device), _abi.stage('istft'):
             packed = self._packed_basis()
             window = self.window.reshape(-1).contiguous()
             _abi.check(_abi.lib().se_istft_fwd(_abi.ptr(spec), _abi.ptr(phase), _abi.ptr(packed),

@@ -50,7 +50,9 @@ struct GemmParams {
   int kblocks[2], kcol0[2];
   int TH, TW, nacc;
   int concat, acc_cols;       // concat: a_hi x [b_hi|b_lo] in one MMA (npad <= 128), 2*npad TMEM columns per accumulator
+  int nsplit, unit_rows;      // split mode: every hi / lo slab travels as nsplit column slices of unit_rows rows
   int a_half, a_slot, b_unit, SA, SB;
+  int ntiles, nbuf, buf_cols;  // persistent tile loop; nbuf TMEM accumulator buffers of buf_cols columns
   int Ho, Wo, Cout2, npad, tmem_cols, y_Cp;
   const float* bias;
   float slope;
@@ -152,11 +154,34 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
   return d;
 }
 
+struct TileCoord { int ci, b, h0, w0, nacc; };
+
+__device__ __forceinline__ TileCoord decode_tile(const GemmParams& p, int tile) {
+  // class-major (heaviest class first), then batch, then row tile, then column tile
+  int ci = 0;
+#pragma unroll
+  for (int c = 1; c < kMaxClasses; ++c)
+    if (c < p.ncls && tile >= p.cls[c].tile_begin) ci = c;
+  const GClass& C = p.cls[ci];
+  int t = tile - C.tile_begin;
+  const int tw = t % C.tiles_w; t /= C.tiles_w;
+  const int th = t % C.tiles_h;
+  TileCoord tc;
+  tc.ci = ci; tc.b = t / C.tiles_h;
+  tc.h0 = th * p.TH * p.nacc; tc.w0 = tw * p.TW;
+  int nacc = (C.Hq_out - tc.h0 + p.TH - 1) / p.TH;
+  tc.nacc = nacc > p.nacc ? p.nacc : nacc;
+  return tc;
+}
+
+// Persistent: grid = #SMs, every CTA walks tiles blockIdx.x, += gridDim.x.  The TMA producer runs
+// ahead across tile boundaries, and with two TMEM accumulator buffers (when nacc * acc_cols <= 256)
+// the epilogue of tile i overlaps the MMAs of tile i+1.
 __global__ void __launch_bounds__(192, 1)
 cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                   const __grid_constant__ CUtensorMap tmW, const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t a_full[2], a_empty[2], b_full[8], b_empty[8], accum_bar;
+  __shared__ __align__(8) uint64_t a_full[2], a_empty[2], b_full[8], b_empty[8], t_full[2], t_empty[2];
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -164,27 +189,13 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
   uint8_t* a_ring = smem;
   uint8_t* b_ring = smem + (size_t)p.SA * p.a_slot;
 
-  // ---- tile decode: class-major, then batch, then row tile, then column tile
-  int ci = 0;
-#pragma unroll
-  for (int c = 1; c < kMaxClasses; ++c)
-    if (c < p.ncls && (int)blockIdx.x >= p.cls[c].tile_begin) ci = c;
-  const GClass& C = p.cls[ci];
-  int t = blockIdx.x - C.tile_begin;
-  const int tw = t % C.tiles_w; t /= C.tiles_w;
-  const int th = t % C.tiles_h;
-  const int b = t / C.tiles_h;
-  const int h0 = th * p.TH * p.nacc, w0 = tw * p.TW;
-  int nacc = (C.Hq_out - h0 + p.TH - 1) / p.TH;
-  if (nacc > p.nacc) nacc = p.nacc;
-
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmX0);
     ptx::prefetch_tmap(&tmX1);
     ptx::prefetch_tmap(&tmW);
     for (int s = 0; s < p.SA; ++s) { ptx::mbar_init(&a_full[s], 1); ptx::mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < p.SB; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
-    ptx::mbar_init(&accum_bar, 1);
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&t_full[s], 1); ptx::mbar_init(&t_empty[s], 4); }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
@@ -195,35 +206,39 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_acc = tmem_base_slot;
-  const int units = p.concat ? 1 : 2;          // B ring units per tap
+  const int units = p.concat ? 1 : 2 * p.nsplit;     // B ring units per tap
 
   if (warp == 0) {
     if (ptx::elect_one()) {
       // ===== TMA producer =====
       uint32_t ia = 0, ib = 0;
-      for (int g = C.g0; g < C.g0 + C.ng; ++g) {
-        const GGroup G = p.groups[g];
-        const CUtensorMap* tm = G.src ? &tmX1 : &tmX0;
-        const int wc = p.col_mul * w0 + G.col_add, hc = p.row_mul * h0 + G.row_add;
-        for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
-          const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
-          ptx::mbar_wait(&a_empty[sa], pa ^ 1u);
-          uint8_t* as = a_ring + (size_t)sa * p.a_slot;
-          ptx::mbar_arrive_expect_tx(&a_full[sa], (uint32_t)p.a_slot);
-          ptx::tma_load_4d(as, tm, &a_full[sa], kbi * 64, wc, hc, b * 2 + 0);
-          ptx::tma_load_4d(as + p.a_half, tm, &a_full[sa], kbi * 64, wc, hc, b * 2 + 1);
-          ++ia;
-          const int kcol = p.kcol0[G.src] + kbi * 64;
-          for (int ti = 0; ti < G.ntaps; ++ti) {
-            const GTap T = p.taps[G.tap0 + ti];
-            for (int u = 0; u < units; ++u) {
-              const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
-              ptx::mbar_wait(&b_empty[sb], pb ^ 1u);
-              uint8_t* bs = b_ring + (size_t)sb * p.b_unit;
-              ptx::mbar_arrive_expect_tx(&b_full[sb], (uint32_t)p.b_unit);
-              // concat: tmW is [taps][2*npad][Cpt] (hi rows then lo rows); split: [taps*2][npad][Cpt]
-              ptx::tma_load_3d(bs, &tmW, &b_full[sb], kcol, 0, p.concat ? T.wslab : T.wslab * 2 + u);
-              ++ib;
+      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(p, tile);
+        const GClass& C = p.cls[tc.ci];
+        for (int g = C.g0; g < C.g0 + C.ng; ++g) {
+          const GGroup G = p.groups[g];
+          const CUtensorMap* tm = G.src ? &tmX1 : &tmX0;
+          const int wc = p.col_mul * tc.w0 + G.col_add, hc = p.row_mul * tc.h0 + G.row_add;
+          for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
+            const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
+            ptx::mbar_wait(&a_empty[sa], pa ^ 1u);
+            uint8_t* as = a_ring + (size_t)sa * p.a_slot;
+            ptx::mbar_arrive_expect_tx(&a_full[sa], (uint32_t)p.a_slot);
+            ptx::tma_load_4d(as, tm, &a_full[sa], kbi * 64, wc, hc, tc.b * 2 + 0);
+            ptx::tma_load_4d(as + p.a_half, tm, &a_full[sa], kbi * 64, wc, hc, tc.b * 2 + 1);
+            ++ia;
+            const int kcol = p.kcol0[G.src] + kbi * 64;
+            for (int ti = 0; ti < G.ntaps; ++ti) {
+              const GTap T = p.taps[G.tap0 + ti];
+              for (int u = 0; u < units; ++u) {
+                const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
+                ptx::mbar_wait(&b_empty[sb], pb ^ 1u);
+                uint8_t* bs = b_ring + (size_t)sb * p.b_unit;
+                ptx::mbar_arrive_expect_tx(&b_full[sb], (uint32_t)p.b_unit);
+                // tmW views wq as [taps * units][unit_rows][Cpt]; unit u = (hi|lo) * nsplit + column slice
+                ptx::tma_load_3d(bs, &tmW, &b_full[sb], kcol, 0, T.wslab * units + u);
+                ++ib;
+              }
             }
           }
         }
@@ -232,114 +247,137 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
   } else if (warp == 1) {
     if (ptx::elect_one()) {
       // ===== MMA issuer =====
-      const uint32_t idesc1 = ptx::make_idesc_bf16_f32(128, p.npad);
+      const uint32_t idesc1 = ptx::make_idesc_bf16_f32(128, p.concat ? p.npad : p.unit_rows);
       const uint32_t idesc2 = ptx::make_idesc_bf16_f32(128, 2 * p.npad);     // concat mode only
       const uint32_t sub_bytes = (uint32_t)(p.TH * p.TW * 128);   // one 128-pixel sub-tile of the halo box
       const uint32_t tw_bytes = (uint32_t)(p.TW * 128);
-      uint32_t ia = 0, ib = 0, started = 0;
-      for (int g = C.g0; g < C.g0 + C.ng; ++g) {
-        const GGroup G = p.groups[g];
-        for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
-          const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
-          ptx::mbar_wait(&a_full[sa], pa);
-          ptx::tc_fence_after();
-          const uint32_t a_base = ptx::smem_u32(a_ring + (size_t)sa * p.a_slot);
-          for (int ti = 0; ti < G.ntaps; ++ti) {
-            const GTap T = p.taps[G.tap0 + ti];
-            const uint32_t a_tap = a_base + (uint32_t)T.arow * tw_bytes;
-            for (int u = 0; u < units; ++u) {
-              const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
-              ptx::mbar_wait(&b_full[sb], pb);
-              ptx::tc_fence_after();
-              const uint64_t bd = make_desc(ptx::smem_u32(b_ring + (size_t)sb * p.b_unit));
-              for (int a = 0; a < nacc; ++a) {
-                const uint64_t a_hi = make_desc(a_tap + (uint32_t)a * sub_bytes);
-                const uint64_t a_lo = make_desc(a_tap + (uint32_t)a * sub_bytes + (uint32_t)p.a_half);
-                const uint32_t d = tmem_acc + (uint32_t)(a * p.acc_cols);
-                const uint32_t first = (started >> a) & 1u;
+      uint32_t ia = 0, ib = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++lt) {
+        const TileCoord tc = decode_tile(p, tile);
+        const GClass& C = p.cls[tc.ci];
+        const uint32_t buf = lt % (uint32_t)p.nbuf, tph = (lt / (uint32_t)p.nbuf) & 1u;
+        ptx::mbar_wait(&t_empty[buf], tph ^ 1u);           // epilogue has drained this accumulator buffer
+        ptx::tc_fence_after();
+        const uint32_t tmem_buf = tmem_acc + buf * (uint32_t)p.buf_cols;
+        uint32_t started = 0;
+        for (int g = C.g0; g < C.g0 + C.ng; ++g) {
+          const GGroup G = p.groups[g];
+          for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
+            const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
+            ptx::mbar_wait(&a_full[sa], pa);
+            ptx::tc_fence_after();
+            const uint32_t a_base = ptx::smem_u32(a_ring + (size_t)sa * p.a_slot);
+            for (int ti = 0; ti < G.ntaps; ++ti) {
+              const GTap T = p.taps[G.tap0 + ti];
+              const uint32_t a_tap = a_base + (uint32_t)T.arow * tw_bytes;
+              for (int u = 0; u < units; ++u) {
+                const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
+                ptx::mbar_wait(&b_full[sb], pb);
+                ptx::tc_fence_after();
+                const uint64_t bd = make_desc(ptx::smem_u32(b_ring + (size_t)sb * p.b_unit));
+                const int sl = p.concat ? 0 : u / p.nsplit;        // 0: b_hi, 1: b_lo
+                const int nh = p.concat ? 0 : u - sl * p.nsplit;   // column slice of the accumulator
+                for (int a = 0; a < tc.nacc; ++a) {
+                  const uint64_t a_hi = make_desc(a_tap + (uint32_t)a * sub_bytes);
+                  const uint64_t a_lo = make_desc(a_tap + (uint32_t)a * sub_bytes + (uint32_t)p.a_half);
+                  const uint32_t d = tmem_buf + (uint32_t)(a * p.acc_cols + nh * p.unit_rows);
+                  const uint32_t bit = 1u << (a * 2 + nh);
+                  const uint32_t first = (started & bit) ? 1u : 0u;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  const uint64_t ko = (uint64_t)(k * 2);          // 16 bf16 = 32 B = 2 descriptor units
-                  if (p.concat) {
-                    // D[:, 0:2N) += a_hi * [b_hi | b_lo]   ;   D[:, 0:N) += a_lo * b_hi
-                    ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc2, first | (uint32_t)(k != 0));
-                    ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, 1);
-                  } else if (u == 0) {
-                    ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, first | (uint32_t)(k != 0));
-                    ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
-                  } else {
-                    ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
+                  for (int k = 0; k < 4; ++k) {
+                    const uint64_t ko = (uint64_t)(k * 2);          // 16 bf16 = 32 B = 2 descriptor units
+                    if (p.concat) {
+                      // D[:, 0:2N) += a_hi * [b_hi | b_lo]   ;   D[:, 0:N) += a_lo * b_hi
+                      ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc2, first | (uint32_t)(k != 0));
+                      ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, 1);
+                    } else if (sl == 0) {
+                      ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, first | (uint32_t)(k != 0));
+                      ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
+                    } else {
+                      ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
+                    }
                   }
+                  started |= bit;
                 }
-                started |= 1u << a;
+                ptx::umma_commit(&b_empty[sb]);
+                ++ib;
               }
-              ptx::umma_commit(&b_empty[sb]);
-              ++ib;
             }
+            ptx::umma_commit(&a_empty[sa]);
+            ++ia;
           }
-          ptx::umma_commit(&a_empty[sa]);
-          ++ia;
         }
+        ptx::umma_commit(&t_full[buf]);
       }
-      ptx::umma_commit(&accum_bar);
     }
   } else {
     // ===== epilogue: TMEM -> registers -> (+bias, activation) -> NCHW fp32 and/or CL2 bf16 =====
     const int q = warp & 3;                       // TMEM lane quarter this warp may access
     const int m = q * 32 + lane;
     const int hl = m / p.TW, wl = m - hl * p.TW;
-    ptx::mbar_wait(&accum_bar, 0);
-    ptx::tc_fence_after();
     const int64_t plane = (int64_t)p.Ho * p.Wo;
     const int cmax = p.y_cl2 != nullptr && p.y_Cp > p.npad ? p.y_Cp : p.npad;
-    const bool have = C.ng > 0;                   // a class no tap reaches is bias-only
-    for (int a = 0; a < nacc; ++a) {
-      const int qh = h0 + a * p.TH + hl, qw = w0 + wl;
-      const int ho = qh * C.oh_mul + C.oh_add, wo = qw * C.ow_mul + C.ow_add;
-      const bool ok = qh < C.Hq_out && qw < C.Wq_out && ho < p.Ho && wo < p.Wo;
-      float* yb = p.y ? p.y + (int64_t)b * p.Cout2 * plane + (int64_t)ho * p.Wo + wo : nullptr;
-      __nv_bfloat16* cb = p.y_cl2 ? p.y_cl2 + ((int64_t)b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
-      const int64_t lo_off = plane * p.y_Cp;
-      const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * p.acc_cols);
-      for (int c0 = 0; c0 < cmax; c0 += 32) {
-        uint32_t r[32], r2[32];
-        if (c0 < p.npad && have) {
-          ptx::tmem_ld_32x32(trow + (uint32_t)c0, r);
-          if (p.concat) ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
-          ptx::tmem_ld_wait();
-        }
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int co = c0 + j;
-          float f = 0.f;
-          if (co < p.Cout2 && have) {
-            f = __uint_as_float(r[j]);
-            if (p.concat) f += __uint_as_float(r2[j]);
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++lt) {
+      const TileCoord tc = decode_tile(p, tile);
+      const GClass& C = p.cls[tc.ci];
+      const uint32_t buf = lt % (uint32_t)p.nbuf, tph = (lt / (uint32_t)p.nbuf) & 1u;
+      ptx::mbar_wait(&t_full[buf], tph);
+      ptx::tc_fence_after();
+      const bool have = C.ng > 0;                 // a class no tap reaches is bias-only
+      const int64_t b = tc.b;
+      for (int a = 0; a < tc.nacc; ++a) {
+        const int qh = tc.h0 + a * p.TH + hl, qw = tc.w0 + wl;
+        const int ho = qh * C.oh_mul + C.oh_add, wo = qw * C.ow_mul + C.ow_add;
+        const bool ok = qh < C.Hq_out && qw < C.Wq_out && ho < p.Ho && wo < p.Wo;
+        float* yb = p.y ? p.y + b * p.Cout2 * plane + (int64_t)ho * p.Wo + wo : nullptr;
+        __nv_bfloat16* cb = p.y_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
+        const int64_t lo_off = plane * p.y_Cp;
+        const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.buf_cols + (uint32_t)(a * p.acc_cols);
+        for (int c0 = 0; c0 < cmax; c0 += 32) {
+          uint32_t r[32], r2[32];
+          if (c0 < p.npad && have) {
+            ptx::tmem_ld_32x32(trow + (uint32_t)c0, r);
+            if (p.concat) ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
+            ptx::tmem_ld_wait();
           }
-          if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
-          v[j] = f > 0.f ? f : f * p.slope;
-        }
-        if (!ok) continue;
-        if (yb != nullptr) {
+          float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c0 + j < p.Cout2) yb[(int64_t)(c0 + j) * plane] = v[j];
-        }
-        if (cb != nullptr && c0 < p.y_Cp) {
-          __align__(16) __nv_bfloat16 hi[32];
-          __align__(16) __nv_bfloat16 lo[32];
+          for (int j = 0; j < 32; ++j) {
+            const int co = c0 + j;
+            float f = 0.f;
+            if (co < p.Cout2 && have) {
+              f = __uint_as_float(r[j]);
+              if (p.concat) f += __uint_as_float(r2[j]);
+            }
+            if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
+            v[j] = f > 0.f ? f : f * p.slope;
+          }
+          if (!ok) continue;
+          if (yb != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) split_bf16(v[j], hi[j], lo[j]);
-          uint4* dh = reinterpret_cast<uint4*>(cb + c0);
-          uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+            for (int j = 0; j < 32; ++j)
+              if (c0 + j < p.Cout2) yb[(int64_t)(c0 + j) * plane] = v[j];
+          }
+          if (cb != nullptr && c0 < p.y_Cp) {
+            __align__(16) __nv_bfloat16 hi[32];
+            __align__(16) __nv_bfloat16 lo[32];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            dh[j] = reinterpret_cast<const uint4*>(hi)[j];
-            dl[j] = reinterpret_cast<const uint4*>(lo)[j];
+            for (int j = 0; j < 32; ++j) split_bf16(v[j], hi[j], lo[j]);
+            uint4* dh = reinterpret_cast<uint4*>(cb + c0);
+            uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              dh[j] = reinterpret_cast<const uint4*>(hi)[j];
+              dl[j] = reinterpret_cast<const uint4*>(lo)[j];
+            }
           }
         }
       }
+      // this warp is done reading the buffer: hand it back to the MMA issuer
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&t_empty[buf]);
     }
   }
   ptx::tc_fence_before();
@@ -469,29 +507,36 @@ static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max)
   return SE_OK;
 }
 
-struct TileChoice { int TH, TW, nacc, SA, SB; double cost; };
+struct TileChoice { int TH, TW, nacc, SA, SB, concat, nsplit; double cost; };
 
 // MMA cost model measured with scripts/mma_rate.cu (cta_group::1, SS operands, 128B swizzle):
 //   cycles(128 x N x 16) = max(N / 2, ~84)
 static inline double mma_cycles(int n) { return fmax(n / 2.0, 84.0); }
+constexpr double kFillBytesPerCycle = 36.0;      // sustained L2 -> SMEM fill per SM
+constexpr double kFillLatency = 2500.0;          // request -> data landed (cycles), covers one B unit
 
-static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int span_max, int npad, bool concat) {
-  TileChoice best{0, 0, 0, 0, 0, 1e300};
+static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int span_max, int npad) {
+  TileChoice best{0, 0, 0, 0, 0, 0, 1, 1e300};
   const int nsm = num_sms();
-  const int acc_cols = concat ? 2 * npad : npad;
-  const int64_t b_unit = (int64_t)acc_cols * 128;                 // bytes of one B ring unit (kb = 64)
-  const int units = concat ? 1 : 2;
-  // one k-step (K = 16) of one tap on one accumulator
-  const double mma_k = concat ? mma_cycles(2 * npad) + mma_cycles(npad) : 3.0 * mma_cycles(npad);
-  for (int TW = 128; TW >= 8; TW >>= 1) {
-    const int TH = 128 / TW;
-    for (int nacc = 1; nacc <= 4; nacc <<= 1) {
-      const int tm_need = (nacc - 1) * acc_cols + (concat ? npad : 0) + round_up(npad, 32);
-      if (tm_need > 512) continue;
-      const int rows = nacc * TH + span_max;
-      if (rows * p.row_mul > 256 || TW * p.col_mul > 256) continue;
-      const int64_t a_slot = 2LL * rows * TW * 128;
-      for (int SA = 2; SA >= 1; --SA) {
+  for (int mode = 0; mode < 3; ++mode) {
+    // mode 0: concat (a_hi x [b_hi|b_lo], a_lo x b_hi); 1: split hi / lo; 2: split + two column slices
+    const bool concat = mode == 0;
+    const int nsplit = mode == 2 ? 2 : 1;
+    if (concat && npad > 128) continue;
+    if (nsplit == 2 && (npad % 32 != 0 || npad < 64)) continue;
+    const int acc_cols = concat ? 2 * npad : npad;
+    const int unit_rows = concat ? 2 * npad : npad / nsplit;
+    const int64_t b_unit = (int64_t)unit_rows * 128;
+    const int units = concat ? 1 : 2 * nsplit;
+    for (int TW = 128; TW >= 8; TW >>= 1) {
+      const int TH = 128 / TW;
+      for (int nacc = 1; nacc <= 4; nacc <<= 1) {
+        const int tm_need = (nacc - 1) * acc_cols + (concat ? npad : 0) + round_up(npad, 32);
+        if (tm_need > 512) continue;
+        const int rows = nacc * TH + span_max;
+        if (rows * p.row_mul > 256 || TW * p.col_mul > 256) continue;
+        const int64_t a_slot = 2LL * rows * TW * 128;
+        const int SA = 2;
         int64_t left = kSmemBudget - 1024 - SA * a_slot;
         if (left < 2 * b_unit) continue;
         int SB = (int)(left / b_unit);
@@ -502,24 +547,31 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
           const int64_t th = (c.Hq_out + nacc * TH - 1) / (nacc * TH), tw = (c.Wq_out + TW - 1) / TW;
           const int64_t n = th * tw * a->B;
           const double acc_avg = (double)((c.Hq_out + TH - 1) / TH) / (double)th;   // live accumulators
+          // per-unit MMA time (4 k-steps); a unit shorter than the fill latency / lookahead stalls the pipe
+          const double floor_u = kFillLatency / (double)(SB - 1);
+          double t_tap;
+          if (concat) t_tap = fmax(acc_avg * 4.0 * (mma_cycles(2 * npad) + mma_cycles(npad)), floor_u);
+          else t_tap = nsplit * (fmax(acc_avg * 4.0 * 2.0 * mma_cycles(unit_rows), floor_u) +
+                                 fmax(acc_avg * 4.0 * mma_cycles(unit_rows), floor_u));
           double per_tile = 0.0;
           for (int g = c.g0; g < c.g0 + c.ng; ++g) {
             const GGroup& G = p.groups[g];
             const int kblocks = (G.src ? a->src_Cp[1] : a->src_Cp[0]) / 64;
-            const double mma = G.ntaps * acc_avg * 4.0 * mma_k;
             const double bytes = (double)a_slot + (double)G.ntaps * units * b_unit;
-            double t = fmax(mma, bytes / 36.0);
-            if (SA == 1) t += a_slot / 36.0 + 1500.0;             // single-buffered A: its load is exposed
-            per_tile += kblocks * t;
+            per_tile += kblocks * fmax(G.ntaps * t_tap, bytes / kFillBytesPerCycle);
           }
-          per_tile += 5000.0 + acc_avg * 128.0 * npad * 4.0 / 20.0;   // prologue + epilogue stores
+          // epilogue (overlapped only with two TMEM buffers) + per-tile bookkeeping
+          const int buf_cols = round_up(nacc * acc_cols, 32);
+          const bool two_bufs = buf_cols + tm_need <= 512;
+          const double epi = acc_avg * 128.0 * npad * 4.0 / 20.0;
+          per_tile += 800.0 + (two_bufs ? 0.25 : 1.0) * epi;
           total += per_tile * n;
           tiles += n;
         }
         const double waves = ceil((double)tiles / nsm);
         double cost = total / (double)tiles * waves;                 // ~cycles, 1 CTA per SM
         if (TW < 32) cost *= 1.0 + 0.03 * (32 / TW);                 // narrow rows: poorly coalesced epilogue
-        if (cost < best.cost) best = TileChoice{TH, TW, nacc, SA, SB, cost};
+        if (cost < best.cost) best = TileChoice{TH, TW, nacc, SA, SB, concat ? 1 : 0, nsplit, cost};
       }
     }
   }
@@ -542,34 +594,38 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   int rc = build_structure(a, p, span_max);
   if (rc != SE_OK) return rc;
   const int npad = round_up(a->Cout2, 16);
-  static const char* force = getenv("SE_GEMM_FORCE");       // "TW,nacc,SA,concat" (tuning aid)
+  static const char* force = getenv("SE_GEMM_FORCE");       // "TW,nacc,mode" (tuning aid; mode 0 concat, 1 split, 2 split x2)
   static const char* dbg_env = getenv("SE_GEMM_DEBUG");     // bit2: print the plan of every launch
   const int dbg = dbg_env ? atoi(dbg_env) : 0;
-  bool concat = npad <= 128;
-  TileChoice tc = choose_tile(a, p, span_max, npad, concat);
+  TileChoice tc = choose_tile(a, p, span_max, npad);
   if (force) {
-    int fTW = 0, fn = 0, fSA = 0, fc = 0;
-    if (sscanf(force, "%d,%d,%d,%d", &fTW, &fn, &fSA, &fc) == 4 && fTW >= 8 && fTW <= 128 && (fc == 0 || npad <= 128)) {
-      const int ac = fc ? 2 * npad : npad;
-      const int64_t as = 2LL * (fn * (128 / fTW) + span_max) * fTW * 128, bu = (int64_t)ac * 128;
-      int64_t left = kSmemBudget - 1024 - fSA * as;
+    int fTW = 0, fn = 0, fm = 0;
+    if (sscanf(force, "%d,%d,%d", &fTW, &fn, &fm) == 3 && fTW >= 8 && fTW <= 128 && fm >= 0 && fm <= 2 &&
+        (fm != 0 || npad <= 128) && (fm != 2 || (npad % 32 == 0 && npad >= 64))) {
+      const int ac = fm == 0 ? 2 * npad : npad, ur = fm == 0 ? 2 * npad : npad / (fm == 2 ? 2 : 1);
+      const int64_t as = 2LL * (fn * (128 / fTW) + span_max) * fTW * 128, bu = (int64_t)ur * 128;
+      int64_t left = kSmemBudget - 1024 - 2 * as;
       int SB = left > 0 ? (int)(left / bu) : 0;
       if (SB > 8) SB = 8;
-      if (SB >= 2 && (fn - 1) * ac + (fc ? npad : 0) + round_up(npad, 32) <= 512) {
-        concat = fc != 0;
-        tc = TileChoice{128 / fTW, fTW, fn, fSA, SB, 0.0};
-      }
+      if (SB >= 2 && (fn - 1) * ac + (fm == 0 ? npad : 0) + round_up(npad, 32) <= 512)
+        tc = TileChoice{128 / fTW, fTW, fn, 2, SB, fm == 0 ? 1 : 0, fm == 2 ? 2 : 1, 0.0};
     }
   }
+  const bool concat = tc.concat != 0;
   if (tc.TW == 0) return fail(SE_ERR_UNSUPPORTED, "%s: no tile shape fits shared memory", nm);
   p.TH = tc.TH; p.TW = tc.TW; p.nacc = tc.nacc;
   p.concat = concat ? 1 : 0; p.acc_cols = concat ? 2 * npad : npad;
+  p.nsplit = tc.nsplit; p.unit_rows = concat ? 2 * npad : npad / tc.nsplit;
   const int rows = tc.nacc * tc.TH + span_max;
   p.a_half = rows * tc.TW * 128; p.a_slot = 2 * p.a_half;
-  p.b_unit = p.acc_cols * 128;
+  p.b_unit = p.unit_rows * 128;
   p.SA = tc.SA; p.SB = tc.SB;
   p.Ho = a->Ho; p.Wo = a->Wo; p.Cout2 = a->Cout2; p.npad = npad; p.y_Cp = a->y_Cp;
-  const int tm_need = (tc.nacc - 1) * p.acc_cols + (concat ? npad : 0) + round_up(npad, 32);
+  // TMEM: nacc accumulators per buffer; two buffers when they fit (epilogue overlaps the next tile's MMAs)
+  const int tm_one = (tc.nacc - 1) * p.acc_cols + (concat ? npad : 0) + round_up(npad, 32);
+  p.buf_cols = round_up(tc.nacc * p.acc_cols, 32);
+  p.nbuf = (p.buf_cols + tm_one <= 512) ? 2 : 1;
+  const int tm_need = (p.nbuf - 1) * p.buf_cols + tm_one;
   p.tmem_cols = 32; while (p.tmem_cols < tm_need) p.tmem_cols <<= 1;
   p.bias = a->bias; p.slope = a->slope; p.y = a->y_nchw; p.y_cl2 = reinterpret_cast<__nv_bfloat16*>(a->y_cl2);
   p.kblocks[0] = a->src_Cp[0] / 64; p.kcol0[0] = 0;
@@ -584,6 +640,7 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   }
   if (ntiles <= 0) return SE_OK;
   if (ntiles > 2147483647LL) return fail(SE_ERR_UNSUPPORTED, "%s: too many tiles", nm);
+  p.ntiles = (int)ntiles;
 
   CUtensorMap tmX[2], tmW;
   for (int i = 0; i < 2; ++i) {
@@ -598,9 +655,9 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     if (rc != SE_OK) return rc;
   }
   {
-    // wq is [taps][2][npad][Cpt]; concat views it as [taps][2*npad][Cpt], split as [taps*2][npad][Cpt]
+    // wq is [taps][2][npad][Cpt], viewed as [taps * units][unit_rows][Cpt]
     const uint64_t Cpt = (uint64_t)a->src_Cp[0] + (a->nsrc == 2 ? a->src_Cp[1] : 0);
-    const uint64_t rows_u = (uint64_t)p.acc_cols, nu = (uint64_t)a->kh * a->kw * (concat ? 1 : 2);
+    const uint64_t rows_u = (uint64_t)p.unit_rows, nu = (uint64_t)a->kh * a->kw * (concat ? 1 : 2 * tc.nsplit);
     uint64_t dims[3] = {Cpt, rows_u, nu};
     uint64_t str[2] = {Cpt * 2, Cpt * 2 * rows_u};
     uint32_t box[3] = {64, (uint32_t)rows_u, 1};
@@ -615,10 +672,11 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     smem_attr = smem;
   }
   if (dbg & 4)
-    fprintf(stderr, "se_cconv_gemm: tr=%d Cp=%d+%d N=%d k=%dx%d s=%dx%d -> TH=%d TW=%d nacc=%d concat=%d SA=%d SB=%d rows=%d smem=%d tmem=%d tiles=%lld ncls=%d\n",
+    fprintf(stderr, "se_cconv_gemm: tr=%d Cp=%d+%d N=%d k=%dx%d s=%dx%d -> TH=%d TW=%d nacc=%d concat=%d nsplit=%d SA=%d SB=%d rows=%d smem=%d tmem=%d nbuf=%d tiles=%lld ncls=%d\n",
             a->transposed, a->src_Cp[0], a->nsrc == 2 ? a->src_Cp[1] : 0, npad, a->kh, a->kw, a->sh, a->sw, tc.TH, tc.TW,
-            tc.nacc, p.concat, tc.SA, tc.SB, rows, smem, p.tmem_cols, (long long)ntiles, p.ncls);
-  cconv_gemm_kernel<<<(unsigned)ntiles, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
+            tc.nacc, p.concat, p.nsplit, tc.SA, tc.SB, rows, smem, p.tmem_cols, p.nbuf, (long long)ntiles, p.ncls);
+  const unsigned grid = (unsigned)(ntiles < num_sms() ? ntiles : num_sms());
+  cconv_gemm_kernel<<<grid, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
   return check_launch("cconv_gemm_kernel");
 }
 

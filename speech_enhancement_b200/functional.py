@@ -38,7 +38,7 @@ def _mask(kind, nr, ni, mr, mi, mask_rows=None):
     args = []
     for t in (nr, ni, mr, mi):
         args += [_abi.ptr(t), t.stride(0), t.stride(1)]
-    with torch.cuda.device(nr.device):
+    with torch.cuda.device(nr.device), _abi.stage('mask'):
         _abi.check(_abi.lib().se_mask_fwd(kind, *args, B, F, T, _abi.ptr(out), _abi.stream_ptr()))
     return out
 

@@ -113,7 +113,7 @@ class ComplexConv(nn.Module):
             raise RuntimeError(f'{type(self).__name__}: expected [B, C, H, W], got {tuple(x.shape)}')
         self._check_supported()
         x = x.contiguous()
-        with torch.cuda.device(x.device):
+        with torch.cuda.device(x.device), _abi.stage('cconv'):
             packed, bias, co, ci, kh, kw = self._packed()
             B, c2, H, W = x.shape
             if c2 != 2 * ci:

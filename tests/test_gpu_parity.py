@@ -265,3 +265,48 @@ def test_models_full_length_vs_oracle(name, cls, args, B):
     mix = tgt + 0.1 * tgt.std() * torch.randn(tgt.shape, generator=torch.Generator().manual_seed(1))
     delta = abs(si_snr_db(wav, mix) - si_snr_db(wav_ref, mix))
     assert delta < 0.01, delta
+
+
+def test_dccrn_fused_chain_matches_modular_path_and_oracle():
+    """eval/no_grad DCCRN runs the chained engine (BN + PReLU + causal pad + skip concat folded into the
+    conv kernels, CL2 between layers); it must agree with the module-by-module path and the CPU oracle."""
+    args = ('dccrn-CL', 400, 100, 512)
+    ref = callers.DCCRN(*args, ops=OPS).eval()
+    sd = seeded_state_dict(ref, seed=5)
+    ref.load_state_dict(sd)
+    ours = callers.DCCRN(*args).eval()
+    ours.load_state_dict(sd)
+    ours.to(DEV)
+    x = synth_noisy_speech(3, 24000, seed=9)
+    with torch.no_grad():
+        _, wav_ref = ref(x)
+        assert ours._use_fused(x.to(DEV))
+        spec_f, wav_f = ours(x.to(DEV))
+        ours.fused = False
+        spec_m, wav_m = ours(x.to(DEV))
+    assert wav_f.shape == wav_m.shape == wav_ref.shape
+    assert rel_l2(wav_f.cpu(), wav_m.cpu()) < 1e-4
+    assert rel_l2(spec_f.cpu(), spec_m.cpu()) < 1e-4
+    assert rel_l2(wav_f.cpu(), wav_ref) < 3e-4
+    assert rel_l2(wav_m.cpu(), wav_ref) < 3e-4
+
+
+def test_cl2_roundtrip_and_two_source_block():
+    from speech_enhancement_b200 import chain
+    x = rand((2, 40, 9, 37), 3).to(DEV)
+    act = chain.cl2_from_nchw(x)
+    assert act.data.shape == (2, 2, 9, 37, 64)
+    assert rel_l2(chain.cl2_to_nchw(act).cpu(), x.cpu()) < 1e-5       # hi + lo keeps ~16 mantissa bits
+    # decoder-style block: complex_concat([x, skip]) -> convT, against the module on the concatenated input
+    m = se.ComplexConvTranspose2d(80, 24, (5, 2), stride=(2, 1), padding=(2, 0), output_padding=(1, 0), bias=True)
+    sd = {k: rand(v.shape, 40 + j, 0.1) for j, (k, v) in enumerate(sorted(m.state_dict().items()))}
+    m.load_state_dict(sd)
+    m.to(DEV)
+    skip = rand((2, 40, 9, 37), 4).to(DEV)
+    with torch.no_grad():
+        y_ref = m(se.complex_concat([x, skip], dim=1))
+        blk = chain.FusedBlock(m, None, torch.nn.LeakyReLU(0.2), src_channels=[40, 40], concat='complex')
+        act_y, y = blk([act, chain.cl2_from_nchw(skip)], out_cl2=True, out_nchw=True)
+    y_ref = torch.nn.functional.leaky_relu(y_ref, 0.2)
+    assert y.shape == y_ref.shape and rel_l2(y.cpu(), y_ref.cpu()) < 5e-5
+    assert rel_l2(chain.cl2_to_nchw(act_y).cpu(), y_ref.cpu()) < 5e-5
