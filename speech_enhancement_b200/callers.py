@@ -375,7 +375,9 @@ class FRCRN(nn.Module):
             if x.shape[-2] < skip.shape[-2]:
                 x = F.pad(x, (0, 0, 0, 1))
             x = layer(complex_concat([x, skip], dim=1))
-        x = self.final_conv(x)                                            # [B, 2, F-2, T]
+        # cuDNN convolutions default to TF32 on CUDA; the parity target is the fp32 reference
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            x = self.final_conv(x)                                        # [B, 2, F-2, T]
         est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, x[:, 0], x[:, 1])
         wav = self.istft(est_spec)
         return est_spec, torch.clamp_(wav, -1, 1)
