@@ -125,8 +125,24 @@ typedef struct se_cconv_args {
   float* y_nchw;               /* [B][Cout2][Ho][Wo] fp32 or NULL                                   */
   void* y_cl2;                 /* bf16 [B][2][Ho][Wo][y_Cp] or NULL                                 */
   int y_Cp;
+  /* optional fp32 output addressing (all zero = NCHW): element (b, co, ho, wo) is written to
+   * y_nchw[b*y_bs + ho*y_hs + pos + y_off] with pos = co*y_cs + wo*y_ws, skipped unless
+   * 0 <= pos + y_off < y_lim (when y_lim > 0) and multiplied by y_scale[pos] (when non-NULL).
+   * This is how the STFT writes [B, 2F, T] from a batch-as-rows image and how the iSTFT scatters
+   * hop phases into the waveform with the window^2 normaliser and the centre crop fused
+   * (conv_stft.py:101-114).                                                                        */
+  int64_t y_bs, y_cs, y_hs, y_ws, y_off, y_lim;
+  const float* y_scale;
 } se_cconv_args;
 SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);
+/* fp32 x[b*xs_b + c*xs_c + h*xs_h + w] -> CL2 (same as se_cl2_from_nchw for arbitrary outer strides). */
+SE_API int se_cl2_from_strided(const float* x, int64_t xs_b, int64_t xs_c, int64_t xs_h, int64_t B, int C, int H,
+                        int W, void* cl2, int Cp, void* stream);
+/* STFT framing for the tensor-core path (replaces the F.pad(reflect) + strided conv1d unfolding of
+ * /root/reference/models/conv_stft.py:60-63): cl2[s][b][q][col] = reflect_pad(x)[b][q*hop + col],
+ * bf16 hi|lo planes, col < hop (zero above), q < Q.  One image row per utterance.              */
+SE_API int se_stft_frames_cl2(const float* x, int64_t B, int64_t L, int hop, int pad, int Q, int Cp, void* cl2,
+                       void* stream);
 SE_API int se_cl2_to_nchw(const void* cl2, int64_t B, int C, int H, int W, int Cp, float* y, void* stream);
 SE_API int64_t se_cconv_wq_elems(int Cout2, int Cp_total, int taps);
 SE_API int se_cconv_prep_weight(const float* packed, int Cout2, int Cin2, int taps, const int* chan_map,

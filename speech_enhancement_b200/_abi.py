@@ -34,6 +34,8 @@ _SIGS = {
     'se_cconvT2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
     'se_cconv_workspace_bytes': (C.c_int64, [_L] + [_I] * 9),
     'se_cl2_from_nchw': (C.c_int, [_P, _L, _I, _I, _I, _P, _I, _P]),
+    'se_cl2_from_strided': (C.c_int, [_P, _L, _L, _L, _L, _I, _I, _I, _P, _I, _P]),
+    'se_stft_frames_cl2': (C.c_int, [_P, _L, _L, _I, _I, _I, _I, _P, _P]),
     'se_cl2_to_nchw': (C.c_int, [_P, _L, _I, _I, _I, _I, _P, _P]),
     'se_cconv_wq_elems': (C.c_int64, [_I, _I, _I]),
     'se_cconv_prep_weight': (C.c_int, [_P, _I, _I, _I, _P, _I, _P, _P]),
@@ -54,7 +56,9 @@ class ConvArgs(C.Structure):
                 ('Cout2', C.c_int), ('kh', C.c_int), ('kw', C.c_int), ('sh', C.c_int), ('sw', C.c_int),
                 ('ph', C.c_int), ('pw', C.c_int), ('Ho', C.c_int), ('Wo', C.c_int),
                 ('wq', C.c_void_p), ('bias', C.c_void_p), ('slope', C.c_float), ('y_nchw', C.c_void_p),
-                ('y_cl2', C.c_void_p), ('y_Cp', C.c_int)]
+                ('y_cl2', C.c_void_p), ('y_Cp', C.c_int),
+                ('y_bs', C.c_int64), ('y_cs', C.c_int64), ('y_hs', C.c_int64), ('y_ws', C.c_int64),
+                ('y_off', C.c_int64), ('y_lim', C.c_int64), ('y_scale', C.c_void_p)]
 
 
 _lib = None

@@ -5,11 +5,36 @@ Same names, constructor and forward signatures, public attributes and state_dict
 the arithmetic runs in libse_b200.so.  The kernels consume the module's own `weight` buffer,
 so a checkpoint with a different basis is honoured.
 """
+import ctypes as C
+
 import numpy as np
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import _abi
+
+# engine selection (class attribute `engine` on both modules):
+#   'auto'  tensor cores whenever the framing fits the conv engine, else the SIMT kernels
+#   'umma'  tensor cores or raise;  'simt' the exact-fp32 SIMT kernels (stft_simt.cu)
+_MAX_TAPS = 16          # ceil(win / hop) taps per launch (se_cconv_gemm allows 49 in total)
+
+
+def _round_up(a, m):
+    return (a + m - 1) // m * m
+
+
+def _tc_ok(win, hop):
+    return hop >= 8 and hop <= 256 and -(-win // hop) <= _MAX_TAPS
+
+
+def _prep_wq(packed, cout2, cin2, taps, Cp):
+    """packed fp32 [cout2][cin2][taps] -> bf16 hi|lo GEMM operand (se_cconv_prep_weight)."""
+    n = _abi.lib().se_cconv_wq_elems(cout2, Cp, taps)
+    wq = torch.empty(n, device=packed.device, dtype=torch.bfloat16)
+    _abi.check(_abi.lib().se_cconv_prep_weight(_abi.ptr(packed), cout2, cin2, taps, None, Cp, _abi.ptr(wq),
+                                               _abi.stream_ptr()))
+    return wq
 
 
 def init_kernels(window_size, fft_size, win_type='hann', inverse=False):
@@ -49,6 +74,46 @@ class ConvSTFT(nn.Module):
         self.center = center
         self.return_mag_phase = return_mag_phase
         self.pad = self.fft_size // 2
+        self._tc = None
+        self._tc_key = None
+
+    engine = 'auto'
+
+    def _tc_operands(self, w):
+        """basis regrouped for the conv engine: the framed convolution (conv_stft.py:63) over hop-sample
+        pixels is a 1 x J convolution with `hop` input channels; output rows go in chunks of <= 256."""
+        key = (w.data_ptr(), w._version, w.device)
+        if self._tc_key != key:
+            c2, _, win = w.shape
+            hop = self.hop_size
+            J = -(-win // hop)
+            Cp = _round_up(hop, 64)
+            wp = F.pad(w[:, 0, :], (0, J * hop - win)).view(c2, J, hop).permute(0, 2, 1).contiguous()
+            chunks = []
+            for c0 in range(0, c2, 256):
+                n = min(256, c2 - c0)
+                chunks.append((c0, n, _prep_wq(wp[c0:c0 + n].contiguous(), n, hop, J, Cp)))
+            self._tc, self._tc_key = (J, Cp, chunks), key
+        return self._tc
+
+    def _forward_tc(self, x, w, out, T, pad):
+        B, L = x.shape
+        c2 = w.shape[0]
+        J, Cp, chunks = self._tc_operands(w)
+        Q = T + J - 1
+        frames = torch.empty((1, 2, B, Q, Cp), device=x.device, dtype=torch.bfloat16)
+        _abi.check(_abi.lib().se_stft_frames_cl2(_abi.ptr(x), B, L, self.hop_size, pad, Q, Cp, _abi.ptr(frames),
+                                                 _abi.stream_ptr()))
+        for c0, n, wq in chunks:
+            a = _abi.ConvArgs()
+            a.transposed, a.B, a.nsrc = 0, 1, 1
+            a.src[0] = frames.data_ptr()
+            a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, B, Q
+            a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.Ho, a.Wo = B, Q, n, 1, J, 1, 1, B, T
+            a.wq, a.bias, a.slope = wq.data_ptr(), None, 1.0
+            a.y_nchw = out.data_ptr() + 4 * c0 * T
+            a.y_cs, a.y_hs, a.y_ws = T, c2 * T, 1            # out[b=row, c0 + co, t]
+            _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
 
     def forward(self, inputs):
         x = _abi.require_cuda_f32(inputs, 'ConvSTFT.forward(inputs)')
@@ -72,10 +137,16 @@ class ConvSTFT(nn.Module):
             raise RuntimeError(f'ConvSTFT: input length {L} is shorter than one window ({win})')
         T = (L + 2 * pad - win) // self.hop_size + 1
         out = torch.empty((B, c2, T), device=x.device, dtype=torch.float32)
+        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size) and B > 0
+        if self.engine == 'umma' and not tc:
+            raise RuntimeError(f'ConvSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
         with torch.cuda.device(x.device), _abi.stage('stft'):
-            _abi.check(_abi.lib().se_stft_fwd(_abi.ptr(x), B, L, _abi.ptr(w), c2, win, self.hop_size,
-                                              self.pad, int(self.center), _abi.ptr(out), T,
-                                              _abi.stream_ptr()))
+            if tc:
+                self._forward_tc(x, w, out, T, pad)
+            else:
+                _abi.check(_abi.lib().se_stft_fwd(_abi.ptr(x), B, L, _abi.ptr(w), c2, win, self.hop_size,
+                                                  self.pad, int(self.center), _abi.ptr(out), T,
+                                                  _abi.stream_ptr()))
             if not self.return_mag_phase:
                 return out
             F = self.fft_size // 2 + 1
@@ -101,6 +172,61 @@ class ConviSTFT(nn.Module):
         self.pad = self.fft_size // 2
         self._packed = None
         self._packed_key = None
+        self._tc = None
+        self._tc_key = None
+        self._scale = {}
+
+    engine = 'auto'
+
+    def _tc_operands(self, w):
+        """inverse basis as a 1 x J convolution over frames with 2F input channels and `hop` output
+        channels (one per hop phase): y[q*hop + r] = sum_j sum_c W[c, j*hop + r] * spec[c, q - j]
+        (the conv_transpose1d of conv_stft.py:99 regrouped by output phase)."""
+        key = (w.data_ptr(), w._version, w.device)
+        if self._tc_key != key:
+            c2, _, win = w.shape
+            hop = self.hop_size
+            J = -(-win // hop)
+            Cp = _round_up(c2, 64)
+            wp = F.pad(w[:, 0, :], (0, J * hop - win)).view(c2, J, hop).flip(1).permute(2, 0, 1).contiguous()
+            self._tc, self._tc_key = (J, Cp, _prep_wq(wp, hop, c2, J, Cp)), key
+            self._scale = {}
+        return self._tc
+
+    def _ola_scale(self, T, J):
+        """1 / (sum of squared windows + 1e-8) per output sample (conv_stft.py:101-106), [Q*hop]."""
+        window = self.window
+        key = (T, window.data_ptr(), window._version, window.device)
+        sc = self._scale.get(key)
+        if sc is None:
+            hop, win = self.hop_size, self.window_size
+            w2 = F.pad(window.reshape(-1).double() ** 2, (0, J * hop - win)).view(J, hop)
+            coff = torch.zeros((T + J - 1, hop), device=window.device, dtype=torch.float64)
+            for j in range(J):
+                coff[j:j + T] += w2[j]
+            sc = (1.0 / (coff.float() + 1e-8)).reshape(-1).contiguous()
+            self._scale = {key: sc}
+        return sc
+
+    def _forward_tc(self, spec, w, out, start, out_len):
+        B, c2, T = spec.shape
+        hop = self.hop_size
+        J, Cp, wq = self._tc_operands(w)
+        scale = self._ola_scale(T, J)
+        img = torch.empty((1, 2, B, T, Cp), device=spec.device, dtype=torch.bfloat16)
+        _abi.check(_abi.lib().se_cl2_from_strided(_abi.ptr(spec), 0, T, c2 * T, 1, c2, B, T, _abi.ptr(img), Cp,
+                                                  _abi.stream_ptr()))
+        a = _abi.ConvArgs()
+        a.transposed, a.B, a.nsrc = 0, 1, 1
+        a.src[0] = img.data_ptr()
+        a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, B, T
+        a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw = B, T, hop, 1, J, 1, 1, 0, J - 1
+        a.Ho, a.Wo = B, T + J - 1
+        a.wq, a.bias, a.slope = wq.data_ptr(), None, 1.0
+        a.y_nchw = out.data_ptr()
+        a.y_cs, a.y_hs, a.y_ws, a.y_off, a.y_lim = 1, out_len, hop, -start, out_len
+        a.y_scale = scale.data_ptr()
+        _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
 
     def _packed_basis(self):
         """inverse basis regrouped per hop phase (se_istft_pack_basis); rebuilt when `weight` changes."""
@@ -143,6 +269,18 @@ class ConviSTFT(nn.Module):
         out_len = max(end - start, 0)
         out = torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
         if out_len == 0 or B == 0:
+            return out
+        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size)
+        if self.engine == 'umma' and not tc:
+            raise RuntimeError(f'ConviSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
+        if tc:
+            with torch.cuda.device(spec.device), _abi.stage('istft'):
+                if phase is not None:
+                    rect = torch.empty((B, c2, T), device=spec.device, dtype=torch.float32)
+                    _abi.check(_abi.lib().se_polar_to_rect(_abi.ptr(spec), _abi.ptr(phase), B, C, T,
+                                                           _abi.ptr(rect), _abi.stream_ptr()))
+                    spec = rect
+                self._forward_tc(spec, w, out, start, out_len)
             return out
         with torch.cuda.device(spec.device), _abi.stage('istft'):
             packed = self._packed_basis()

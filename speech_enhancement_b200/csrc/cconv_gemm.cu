@@ -58,6 +58,8 @@ struct GemmParams {
   float slope;
   float* y;
   __nv_bfloat16* y_cl2;
+  int64_t y_bs, y_cs, y_hs, y_ws, y_off, y_lim;   // fp32 output addressing (defaults = NCHW)
+  const float* y_scale;                           // optional per-position scale (iSTFT normaliser)
 };
 
 // ------------------------------------------------------------------------------ prep kernels
@@ -68,7 +70,8 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bflo
 
 // NCHW fp32 -> CL2.  grid: (ceil(W/32), H, B*(Cp/64)); block 256
 __global__ void __launch_bounds__(256)
-cl2_from_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xs, int C, int H, int W, int Cp) {
+cl2_from_nchw_kernel(const float* __restrict__ x, int64_t xs_b, int64_t xs_c, int64_t xs_h,
+                     __nv_bfloat16* __restrict__ xs, int C, int H, int W, int Cp) {
   __shared__ __align__(16) __nv_bfloat16 s_hi[32][64 + 8];
   __shared__ __align__(16) __nv_bfloat16 s_lo[32][64 + 8];
   const int cblocks = Cp / 64;
@@ -79,7 +82,7 @@ cl2_from_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xs
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     int cl = ty + 8 * i, c = cb * 64 + cl;
-    float v = (pix_ok && c < C) ? __ldg(x + (((int64_t)b * C + c) * H + h) * W + w0 + tx) : 0.f;
+    float v = (pix_ok && c < C) ? __ldg(x + b * xs_b + c * xs_c + h * xs_h + w0 + tx) : 0.f;
     split_bf16(v, s_hi[tx][cl], s_lo[tx][cl]);
   }
   __syncthreads();
@@ -330,7 +333,8 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
         const int qh = tc.h0 + a * p.TH + hl, qw = tc.w0 + wl;
         const int ho = qh * C.oh_mul + C.oh_add, wo = qw * C.ow_mul + C.ow_add;
         const bool ok = qh < C.Hq_out && qw < C.Wq_out && ho < p.Ho && wo < p.Wo;
-        float* yb = p.y ? p.y + b * p.Cout2 * plane + (int64_t)ho * p.Wo + wo : nullptr;
+        float* yb = p.y ? p.y + b * p.y_bs + (int64_t)ho * p.y_hs : nullptr;
+        const int64_t ypos = (int64_t)wo * p.y_ws;           // + co * y_cs: position inside the (b, ho) row block
         __nv_bfloat16* cb = p.y_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
         const int64_t lo_off = plane * p.y_Cp;
         const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.buf_cols + (uint32_t)(a * p.acc_cols);
@@ -356,8 +360,14 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
           if (!ok) continue;
           if (yb != nullptr) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (c0 + j < p.Cout2) yb[(int64_t)(c0 + j) * plane] = v[j];
+            for (int j = 0; j < 32; ++j) {
+              if (c0 + j < p.Cout2) {
+                const int64_t pos = ypos + (int64_t)(c0 + j) * p.y_cs;
+                const int64_t dst = pos + p.y_off;
+                if (p.y_lim == 0 || (dst >= 0 && dst < p.y_lim))
+                  yb[dst] = p.y_scale ? v[j] * __ldg(p.y_scale + pos) : v[j];
+              }
+            }
           }
           if (cb != nullptr && c0 < p.y_Cp) {
             __align__(16) __nv_bfloat16 hi[32];
@@ -628,6 +638,13 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   const int tm_need = (p.nbuf - 1) * p.buf_cols + tm_one;
   p.tmem_cols = 32; while (p.tmem_cols < tm_need) p.tmem_cols <<= 1;
   p.bias = a->bias; p.slope = a->slope; p.y = a->y_nchw; p.y_cl2 = reinterpret_cast<__nv_bfloat16*>(a->y_cl2);
+  if (a->y_cs != 0 || a->y_ws != 0) {
+    p.y_bs = a->y_bs; p.y_cs = a->y_cs; p.y_hs = a->y_hs; p.y_ws = a->y_ws; p.y_off = a->y_off; p.y_lim = a->y_lim;
+  } else {
+    const int64_t plane = (int64_t)a->Ho * a->Wo;
+    p.y_bs = (int64_t)a->Cout2 * plane; p.y_cs = plane; p.y_hs = a->Wo; p.y_ws = 1; p.y_off = 0; p.y_lim = 0;
+  }
+  p.y_scale = a->y_scale;
   p.kblocks[0] = a->src_Cp[0] / 64; p.kcol0[0] = 0;
   p.kblocks[1] = a->nsrc == 2 ? a->src_Cp[1] / 64 : 0; p.kcol0[1] = a->src_Cp[0];
   int64_t ntiles = 0;
@@ -751,8 +768,74 @@ extern "C" int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, 
   if (B == 0) return SE_OK;
   dim3 grid((unsigned)((W + 31) / 32), (unsigned)H, (unsigned)(B * (Cp / 64)));
   if (grid.y > 65535 || grid.z > 65535) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_nchw: tensor too large");
-  se::cl2_from_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<__nv_bfloat16*>(cl2), C, H, W, Cp);
+  se::cl2_from_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      x, (int64_t)C * H * W, (int64_t)H * W, (int64_t)W, reinterpret_cast<__nv_bfloat16*>(cl2), C, H, W, Cp);
   return se::check_launch("se_cl2_from_nchw");
+}
+
+// Same conversion from an fp32 tensor addressed as x[b*xs_b + c*xs_c + h*xs_h + w] (unit stride
+// along w).  The iSTFT uses it to view a [B, 2F, T] spectrogram as one image whose rows are the
+// utterances: B=1, C=2F (xs_c = T), H=batch (xs_h = 2F*T).
+extern "C" int se_cl2_from_strided(const float* x, int64_t xs_b, int64_t xs_c, int64_t xs_h, int64_t B, int C,
+                                   int H, int W, void* cl2, int Cp, void* stream) {
+  SE_REQUIRE(x && cl2, "se_cl2_from_strided: null pointer");
+  SE_REQUIRE(B >= 0 && C > 0 && H > 0 && W > 0 && Cp >= C && Cp % 64 == 0, "se_cl2_from_strided: bad dims");
+  if (B == 0) return SE_OK;
+  dim3 grid((W + 31) / 32, H, (unsigned)(B * (Cp / 64)));
+  if (grid.y > 65535 || grid.z > 65535) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_strided: tensor too large");
+  se::cl2_from_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      x, xs_b, xs_c, xs_h, reinterpret_cast<__nv_bfloat16*>(cl2), C, H, W, Cp);
+  return se::check_launch("se_cl2_from_strided");
+}
+
+// STFT framing for the tensor-core path: reflect-pad (conv_stft.py:60-62) and cut the signal into
+// hop-sample pixels, split into bf16 hi|lo planes: cl2[s][b][q][col] = xpad[b][q*hop + col]
+// (col < hop, else 0) -- a CL2 image with one row per utterance and `hop` channels, so that the
+// framed convolution (conv_stft.py:63) is a 1 x ceil(win/hop) convolution over it.
+namespace se {
+__global__ void __launch_bounds__(256)
+stft_frames_cl2_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t B, int64_t L, int hop,
+                       int pad, int Q, int Cp) {
+  const int vec = Cp / 8;
+  const int64_t total = B * Q * vec;
+  const int64_t plane = B * Q * (int64_t)Cp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int v8 = (int)(i % vec);
+    const int64_t r = i / vec;
+    const int q = (int)(r % Q);
+    const int64_t b = r / Q;
+    const float* xb = x + b * L;
+    __align__(16) __nv_bfloat16 hi[8], lo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int col = v8 * 8 + j;
+      float val = 0.f;
+      if (col < hop) {
+        int64_t n = (int64_t)q * hop + col - pad;
+        if (n < 0) n = -n;
+        if (n >= L) n = 2 * (L - 1) - n;
+        if (n >= 0 && n < L && (int64_t)q * hop + col < L + 2 * (int64_t)pad) val = __ldg(xb + n);
+      }
+      split_bf16(val, hi[j], lo[j]);
+    }
+    const int64_t off = (b * Q + q) * Cp + v8 * 8;
+    *reinterpret_cast<uint4*>(out + off) = *reinterpret_cast<const uint4*>(hi);
+    *reinterpret_cast<uint4*>(out + plane + off) = *reinterpret_cast<const uint4*>(lo);
+  }
+}
+}  // namespace se
+
+extern "C" int se_stft_frames_cl2(const float* x, int64_t B, int64_t L, int hop, int pad, int Q, int Cp, void* cl2,
+                                  void* stream) {
+  SE_REQUIRE(x && cl2, "se_stft_frames_cl2: null pointer");
+  SE_REQUIRE(B >= 0 && L > 0 && hop > 0 && pad >= 0 && pad < L && Q > 0 && Cp >= hop && Cp % 64 == 0,
+             "se_stft_frames_cl2: bad dims");
+  if (B == 0) return SE_OK;
+  const int64_t total = B * Q * (Cp / 8);
+  const unsigned blocks = (unsigned)std::min<int64_t>((total + 255) / 256, 148 * 16);
+  se::stft_frames_cl2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      x, reinterpret_cast<__nv_bfloat16*>(cl2), B, L, hop, pad, Q, Cp);
+  return se::check_launch("se_stft_frames_cl2");
 }
 
 extern "C" int se_cl2_to_nchw(const void* cl2, int64_t B, int C, int H, int W, int Cp, float* y, void* stream) {

@@ -18,6 +18,13 @@ from cases import STFT_CASES, CONV_CASES
 pytestmark = pytest.mark.gpu
 DEV = 'cuda:0'
 TOL_EXACT = 1e-5
+TOL_STFT = {'simt': 1e-5, 'umma': 3e-5}      # exact-fp32 SIMT kernels / bf16x3 tensor-core framing
+
+
+def _stft_pair(engine, *args, **kw):
+    st, ist = se.ConvSTFT(*args, **kw).to(DEV), se.ConviSTFT(*args, **kw).to(DEV)
+    st.engine = ist.engine = engine
+    return st, ist
 
 
 @pytest.fixture(autouse=True)
@@ -25,63 +32,71 @@ def _lib(built_lib):
     assert built_lib.se_device_ok() == 1, 'these tests need a compute-capability 10.x device'
 
 
+@pytest.mark.parametrize('engine', ['simt', 'umma'])
 @pytest.mark.parametrize('i', range(len(STFT_CASES)))
-def test_stft_istft_golden(i):
+def test_stft_istft_golden(i, engine):
     g = golden('stft')
+    tol = TOL_STFT[engine]
     win, hop, fft, L = STFT_CASES[i]
     x = rand((2, L), 100 + i, 0.1).to(DEV)
-    st, ist = se.ConvSTFT(win, hop, fft).to(DEV), se.ConviSTFT(win, hop, fft).to(DEV)
+    st, ist = _stft_pair(engine, win, hop, fft)
     with torch.no_grad():
         spec = st(x)
         assert spec.shape == g[f'{i}_spec'].shape
-        assert rel_l2(spec.cpu(), g[f'{i}_spec']) < TOL_EXACT
+        assert rel_l2(spec.cpu(), g[f'{i}_spec']) < tol
         gs = torch.from_numpy(g[f'{i}_spec']).to(DEV)
         wav = ist(gs)
-        assert wav.shape == g[f'{i}_wav'].shape and rel_l2(wav.cpu(), g[f'{i}_wav']) < TOL_EXACT
+        assert wav.shape == g[f'{i}_wav'].shape and rel_l2(wav.cpu(), g[f'{i}_wav']) < tol
         wav2 = ist(gs, output_length=L - 7)
-        assert wav2.shape == g[f'{i}_wav_len'].shape and rel_l2(wav2.cpu(), g[f'{i}_wav_len']) < TOL_EXACT
+        assert wav2.shape == g[f'{i}_wav_len'].shape and rel_l2(wav2.cpu(), g[f'{i}_wav_len']) < tol
         # round trip (size-independent property): istft(stft(x)) == x[:L']
         rt = ist(spec)
-        assert rel_l2(rt.cpu(), x[:, :rt.shape[1]].cpu()) < 1e-5
+        assert rel_l2(rt.cpu(), x[:, :rt.shape[1]].cpu()) < tol
         if f'{i}_mags' in g:
-            mags, phase = se.ConvSTFT(win, hop, fft, return_mag_phase=True).to(DEV)(x)
-            assert rel_l2(mags.cpu(), g[f'{i}_mags']) < TOL_EXACT
+            stm = se.ConvSTFT(win, hop, fft, return_mag_phase=True).to(DEV)
+            stm.engine = engine
+            mags, phase = stm(x)
+            assert rel_l2(mags.cpu(), g[f'{i}_mags']) < tol
             gm, gp = torch.from_numpy(g[f'{i}_mags']).to(DEV), torch.from_numpy(g[f'{i}_phase']).to(DEV)
             d = torch.remainder(phase - gp + np.pi, 2 * np.pi) - np.pi
-            assert (d.abs() * (gm > 1e-3)).max() < 1e-3
-            assert rel_l2(ist(gm, gp).cpu(), g[f'{i}_wav_polar']) < TOL_EXACT
+            # phase of a weak bin amplifies the spectrum error by 1/|bin|: looser for the bf16x3 engine
+            assert (d.abs() * (gm > 1e-3)).max() < (1e-3 if engine == 'simt' else 5e-3)
+            assert rel_l2(ist(gm, gp).cpu(), g[f'{i}_wav_polar']) < tol
 
 
-def test_stft_input_forms_and_not_centered():
+@pytest.mark.parametrize('engine', ['simt', 'umma'])
+def test_stft_input_forms_and_not_centered(engine):
     g = golden('stft')
+    tol = TOL_STFT[engine]
     x = rand((3000,), 77, 0.1).to(DEV)
-    st = se.ConvSTFT(400, 100, 512, center=False).to(DEV)
-    ist = se.ConviSTFT(400, 100, 512, center=False).to(DEV)
+    st, ist = _stft_pair(engine, 400, 100, 512, center=False)
     with torch.no_grad():
         spec = st(x)
-        assert spec.shape == g['nc_spec'].shape and rel_l2(spec.cpu(), g['nc_spec']) < TOL_EXACT
+        assert spec.shape == g['nc_spec'].shape and rel_l2(spec.cpu(), g['nc_spec']) < tol
         assert torch.equal(spec, st(x[None, None, :])) and torch.equal(spec, st(x[None, :]))
         wav = ist(spec)
         # without centring the first/last samples divide by window^2 ~ 0 (+1e-8): ill-conditioned edges
-        assert wav.shape == g['nc_wav'].shape and rel_l2(wav.cpu(), g['nc_wav']) < 1e-4
-        assert rel_l2(wav[:, 100:-100].cpu(), g['nc_wav'][:, 100:-100]) < TOL_EXACT
+        assert wav.shape == g['nc_wav'].shape and rel_l2(wav.cpu(), g['nc_wav']) < (1e-4 if engine == 'simt' else 2e-3)
+        assert rel_l2(wav[:, 100:-100].cpu(), g['nc_wav'][:, 100:-100]) < tol
     with pytest.raises(RuntimeError):
         se.ConvSTFT(400, 100, 512).to(DEV)(torch.zeros(1, 100, device=DEV))     # reflect pad > signal
 
 
 @pytest.mark.parametrize('win,hop,fft,L,B', [(400, 100, 512, 64000, 8), (512, 128, 512, 64000, 8),
                                              (320, 160, 640, 64000, 4), (400, 100, 512, 160000, 2)])
-def test_stft_full_size_vs_oracle(win, hop, fft, L, B):
+@pytest.mark.parametrize('engine', ['simt', 'umma'])
+def test_stft_full_size_vs_oracle(win, hop, fft, L, B, engine):
+    tol = TOL_STFT[engine]
     x = synth_noisy_speech(B, L, seed=3)
-    st, ist = se.ConvSTFT(win, hop, fft).to(DEV), se.ConviSTFT(win, hop, fft).to(DEV)
+    st, ist = _stft_pair(engine, win, hop, fft)
     with torch.no_grad():
         spec = st(x.to(DEV))
         spec_ref = oracle.stft_ref(x, st.weight.cpu(), hop, fft // 2)
-        assert spec.shape == spec_ref.shape and rel_l2(spec.cpu(), spec_ref) < TOL_EXACT
+        assert spec.shape == spec_ref.shape and rel_l2(spec.cpu(), spec_ref) < tol
         wav = ist(spec)
         wav_ref = oracle.istft_ref(spec_ref, ist.weight.cpu(), ist.window.cpu(), hop, fft // 2)
-        assert wav.shape == wav_ref.shape and rel_l2(wav.cpu(), wav_ref) < TOL_EXACT
-        assert rel_l2(wav.cpu(), x[:, :wav.shape[1]]) < 1e-5
+        assert wav.shape == wav_ref.shape and rel_l2(wav.cpu(), wav_ref) < tol
+        assert rel_l2(wav.cpu(), x[:, :wav.shape[1]]) < tol
 
 
 def _conv_case(i, engine):
