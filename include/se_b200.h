@@ -172,6 +172,14 @@ SE_API int se_mask_fwd(int kind,
 SE_API int se_polar_to_rect(const float* mags, const float* phase, int64_t B, int F, int64_t T,
                      float* spec, void* stream);
 
+/* ---- recurrent half of an LSTM layer (replaces the time-step loop of the four
+ * nn.LSTM passes of /root/reference/models/modules/complex_nn.py:131-142) -------------------------
+ * pre_gates [N][T][4H] = W_ih x + b_ih + b_hh (gate order i|f|g|o), w_hh [4H][H], zero initial state;
+ * writes h_out [N][T][H].  One persistent CTA per batch row(s), no inter-CTA synchronisation.     */
+SE_API int se_lstm_rec_supported(int H);
+SE_API int se_lstm_rec_fwd(const float* pre_gates, const float* w_hh, int64_t N, int64_t T, int H, float* h_out,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

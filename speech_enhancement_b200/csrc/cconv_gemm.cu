@@ -60,6 +60,7 @@ struct GemmParams {
   __nv_bfloat16* y_cl2;
   int64_t y_bs, y_cs, y_hs, y_ws, y_off, y_lim;   // fp32 output addressing (defaults = NCHW)
   const float* y_scale;                           // optional per-position scale (iSTFT normaliser)
+  unsigned long long* prof;                       // SE_GEMM_PROF=1: per-role wait/work cycle counters (tuning aid)
 };
 
 // ------------------------------------------------------------------------------ prep kernels
@@ -159,6 +160,14 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 
 struct TileCoord { int ci, b, h0, w0, nacc; };
 
+// mbarrier wait that charges its duration to `acc` when profiling is on
+__device__ __forceinline__ void timed_wait(uint64_t* bar, uint32_t parity, bool prof, unsigned long long& acc) {
+  if (!prof) { ptx::mbar_wait(bar, parity); return; }
+  const long long t0 = clock64();
+  ptx::mbar_wait(bar, parity);
+  acc += (unsigned long long)(clock64() - t0);
+}
+
 __device__ __forceinline__ TileCoord decode_tile(const GemmParams& p, int tile) {
   // class-major (heaviest class first), then batch, then row tile, then column tile
   int ci = 0;
@@ -180,6 +189,7 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmParams& p, int tile) 
 // Persistent: grid = #SMs, every CTA walks tiles blockIdx.x, += gridDim.x.  The TMA producer runs
 // ahead across tile boundaries, and with two TMEM accumulator buffers (when nacc * acc_cols <= 256)
 // the epilogue of tile i overlaps the MMAs of tile i+1.
+template <bool kConcat>
 __global__ void __launch_bounds__(192, 1)
 cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                   const __grid_constant__ CUtensorMap tmW, const __grid_constant__ GemmParams p) {
@@ -209,12 +219,16 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_acc = tmem_base_slot;
-  const int units = p.concat ? 1 : 2 * p.nsplit;     // B ring units per tap
+  const int units = kConcat ? 1 : 2 * p.nsplit;      // B ring units per tap
 
   if (warp == 0) {
     if (ptx::elect_one()) {
       // ===== TMA producer =====
-      uint32_t ia = 0, ib = 0;
+      uint32_t sa = 0, pa = 1, sb = 0, pb = 1;            // ring slot + the parity its "empty" barrier must show
+      const uint32_t SB = (uint32_t)p.SB;
+      const bool prof = p.prof != nullptr;
+      unsigned long long w_a = 0, w_b = 0;
+      const long long t_start = prof ? clock64() : 0;
       for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
         const TileCoord tc = decode_tile(p, tile);
         const GClass& C = p.cls[tc.ci];
@@ -222,95 +236,139 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
           const GGroup G = p.groups[g];
           const CUtensorMap* tm = G.src ? &tmX1 : &tmX0;
           const int wc = p.col_mul * tc.w0 + G.col_add, hc = p.row_mul * tc.h0 + G.row_add;
-          for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
-            const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
-            ptx::mbar_wait(&a_empty[sa], pa ^ 1u);
+          const int nkb = p.kblocks[G.src], kcol0 = p.kcol0[G.src];
+          for (int kbi = 0; kbi < nkb; ++kbi) {
+            timed_wait(&a_empty[sa], pa, prof, w_a);
             uint8_t* as = a_ring + (size_t)sa * p.a_slot;
             ptx::mbar_arrive_expect_tx(&a_full[sa], (uint32_t)p.a_slot);
             ptx::tma_load_4d(as, tm, &a_full[sa], kbi * 64, wc, hc, tc.b * 2 + 0);
             ptx::tma_load_4d(as + p.a_half, tm, &a_full[sa], kbi * 64, wc, hc, tc.b * 2 + 1);
-            ++ia;
-            const int kcol = p.kcol0[G.src] + kbi * 64;
+            if (++sa == 2) { sa = 0; pa ^= 1u; }
+            const int kcol = kcol0 + kbi * 64;
             for (int ti = 0; ti < G.ntaps; ++ti) {
-              const GTap T = p.taps[G.tap0 + ti];
+              const int slab0 = p.taps[G.tap0 + ti].wslab * units;
               for (int u = 0; u < units; ++u) {
-                const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
-                ptx::mbar_wait(&b_empty[sb], pb ^ 1u);
+                timed_wait(&b_empty[sb], pb, prof, w_b);
                 uint8_t* bs = b_ring + (size_t)sb * p.b_unit;
                 ptx::mbar_arrive_expect_tx(&b_full[sb], (uint32_t)p.b_unit);
                 // tmW views wq as [taps * units][unit_rows][Cpt]; unit u = (hi|lo) * nsplit + column slice
-                ptx::tma_load_3d(bs, &tmW, &b_full[sb], kcol, 0, T.wslab * units + u);
-                ++ib;
+                ptx::tma_load_3d(bs, &tmW, &b_full[sb], kcol, 0, slab0 + u);
+                if (++sb == SB) { sb = 0; pb ^= 1u; }
               }
             }
           }
         }
       }
+      if (prof) {
+        atomicAdd(p.prof + 0, (unsigned long long)(clock64() - t_start));
+        atomicAdd(p.prof + 1, w_a);
+        atomicAdd(p.prof + 2, w_b);
+      }
     }
   } else if (warp == 1) {
     if (ptx::elect_one()) {
       // ===== MMA issuer =====
-      const uint32_t idesc1 = ptx::make_idesc_bf16_f32(128, p.concat ? p.npad : p.unit_rows);
+      // One thread issues every MMA, so its own instruction stream is on the critical path: a 128x256x16
+      // MMA retires in 128 cycles, and the first version of this loop (64-bit descriptor arithmetic,
+      // div/mod ring indices, mode branches inside the k loop) spent ~230 cycles of scalar code per
+      // MMA (SE_GEMM_PROF).  Everything below is 32-bit descriptor-low-word arithmetic on running
+      // counters; the descriptor high word is the constant kDescHi.
+      const uint32_t idesc1 = ptx::make_idesc_bf16_f32(128, kConcat ? p.npad : p.unit_rows);
       const uint32_t idesc2 = ptx::make_idesc_bf16_f32(128, 2 * p.npad);     // concat mode only
-      const uint32_t sub_bytes = (uint32_t)(p.TH * p.TW * 128);   // one 128-pixel sub-tile of the halo box
-      const uint32_t tw_bytes = (uint32_t)(p.TW * 128);
-      uint32_t ia = 0, ib = 0, lt = 0;
+      const uint32_t sub16 = (uint32_t)(p.TH * p.TW * 128) >> 4;   // one 128-pixel sub-tile of the halo box
+      const uint32_t tw16 = (uint32_t)(p.TW * 128) >> 4;
+      const uint32_t half16 = (uint32_t)p.a_half >> 4;
+      const uint32_t a_ring32 = (ptx::smem_u32(a_ring) >> 4) | 0x10000u, a_slot16 = (uint32_t)p.a_slot >> 4;
+      const uint32_t b_ring32 = (ptx::smem_u32(b_ring) >> 4) | 0x10000u, b_unit16 = (uint32_t)p.b_unit >> 4;
+      const uint32_t SB = (uint32_t)p.SB, acc_cols = (uint32_t)p.acc_cols, unit_rows = (uint32_t)p.unit_rows;
+      const int nsplit = p.nsplit;
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0, lt = 0;
+      const bool prof = p.prof != nullptr;
+      unsigned long long w_t = 0, w_a = 0, w_b = 0;
+      const long long t_start = prof ? clock64() : 0;
       for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++lt) {
         const TileCoord tc = decode_tile(p, tile);
         const GClass& C = p.cls[tc.ci];
         const uint32_t buf = lt % (uint32_t)p.nbuf, tph = (lt / (uint32_t)p.nbuf) & 1u;
-        ptx::mbar_wait(&t_empty[buf], tph ^ 1u);           // epilogue has drained this accumulator buffer
+        timed_wait(&t_empty[buf], tph ^ 1u, prof, w_t);    // epilogue has drained this accumulator buffer
         ptx::tc_fence_after();
         const uint32_t tmem_buf = tmem_acc + buf * (uint32_t)p.buf_cols;
-        uint32_t started = 0;
+        const uint32_t nacc = (uint32_t)tc.nacc;
+        uint32_t keep = 0;                                  // 0 until the first tap of the tile has been issued
         for (int g = C.g0; g < C.g0 + C.ng; ++g) {
           const GGroup G = p.groups[g];
-          for (int kbi = 0; kbi < p.kblocks[G.src]; ++kbi) {
-            const uint32_t sa = ia % p.SA, pa = (ia / p.SA) & 1u;
-            ptx::mbar_wait(&a_full[sa], pa);
+          const int nkb = p.kblocks[G.src];
+          for (int kbi = 0; kbi < nkb; ++kbi) {
+            timed_wait(&a_full[sa], pa, prof, w_a);
             ptx::tc_fence_after();
-            const uint32_t a_base = ptx::smem_u32(a_ring + (size_t)sa * p.a_slot);
+            const uint32_t a_base32 = a_ring32 + sa * a_slot16;
             for (int ti = 0; ti < G.ntaps; ++ti) {
-              const GTap T = p.taps[G.tap0 + ti];
-              const uint32_t a_tap = a_base + (uint32_t)T.arow * tw_bytes;
-              for (int u = 0; u < units; ++u) {
-                const uint32_t sb = ib % p.SB, pb = (ib / p.SB) & 1u;
-                ptx::mbar_wait(&b_full[sb], pb);
+              const uint32_t a_tap32 = a_base32 + (uint32_t)p.taps[G.tap0 + ti].arow * tw16;
+              if (kConcat) {
+                timed_wait(&b_full[sb], pb, prof, w_b);
                 ptx::tc_fence_after();
-                const uint64_t bd = make_desc(ptx::smem_u32(b_ring + (size_t)sb * p.b_unit));
-                const int sl = p.concat ? 0 : u / p.nsplit;        // 0: b_hi, 1: b_lo
-                const int nh = p.concat ? 0 : u - sl * p.nsplit;   // column slice of the accumulator
-                for (int a = 0; a < tc.nacc; ++a) {
-                  const uint64_t a_hi = make_desc(a_tap + (uint32_t)a * sub_bytes);
-                  const uint64_t a_lo = make_desc(a_tap + (uint32_t)a * sub_bytes + (uint32_t)p.a_half);
-                  const uint32_t d = tmem_buf + (uint32_t)(a * p.acc_cols + nh * p.unit_rows);
-                  const uint32_t bit = 1u << (a * 2 + nh);
-                  const uint32_t first = (started & bit) ? 1u : 0u;
+                const uint32_t b32 = b_ring32 + sb * b_unit16;
+                uint32_t ah = a_tap32, d = tmem_buf;
+                for (uint32_t a = 0; a < nacc; ++a, ah += sub16, d += acc_cols) {
+                  const uint32_t al = ah + half16;
+                  // D[:, 0:2N) += a_hi * [b_hi | b_lo]   ;   D[:, 0:N) += a_lo * b_hi
+                  ptx::umma_bf16_lo32(d, ah, b32, idesc2, keep);
+                  ptx::umma_bf16_lo32(d, al, b32, idesc1, 1);
 #pragma unroll
-                  for (int k = 0; k < 4; ++k) {
-                    const uint64_t ko = (uint64_t)(k * 2);          // 16 bf16 = 32 B = 2 descriptor units
-                    if (p.concat) {
-                      // D[:, 0:2N) += a_hi * [b_hi | b_lo]   ;   D[:, 0:N) += a_lo * b_hi
-                      ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc2, first | (uint32_t)(k != 0));
-                      ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, 1);
-                    } else if (sl == 0) {
-                      ptx::umma_bf16(d, a_lo + ko, bd + ko, idesc1, first | (uint32_t)(k != 0));
-                      ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
-                    } else {
-                      ptx::umma_bf16(d, a_hi + ko, bd + ko, idesc1, 1);
-                    }
+                  for (uint32_t k = 2; k < 8; k += 2) {     // 16 bf16 = 32 B = 2 descriptor units
+                    ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc2, 1);
+                    ptx::umma_bf16_lo32(d, al + k, b32 + k, idesc1, 1);
                   }
-                  started |= bit;
                 }
                 ptx::umma_commit(&b_empty[sb]);
-                ++ib;
+                if (++sb == SB) { sb = 0; pb ^= 1u; }
+              } else {
+                // b_hi units (one per column slice): D += a_lo * b_hi + a_hi * b_hi
+                for (int nh = 0; nh < nsplit; ++nh) {
+                  timed_wait(&b_full[sb], pb, prof, w_b);
+                  ptx::tc_fence_after();
+                  const uint32_t b32 = b_ring32 + sb * b_unit16;
+                  uint32_t ah = a_tap32, d = tmem_buf + (uint32_t)nh * unit_rows;
+                  for (uint32_t a = 0; a < nacc; ++a, ah += sub16, d += acc_cols) {
+                    const uint32_t al = ah + half16;
+                    ptx::umma_bf16_lo32(d, al, b32, idesc1, keep);
+                    ptx::umma_bf16_lo32(d, ah, b32, idesc1, 1);
+#pragma unroll
+                    for (uint32_t k = 2; k < 8; k += 2) {
+                      ptx::umma_bf16_lo32(d, al + k, b32 + k, idesc1, 1);
+                      ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc1, 1);
+                    }
+                  }
+                  ptx::umma_commit(&b_empty[sb]);
+                  if (++sb == SB) { sb = 0; pb ^= 1u; }
+                }
+                // b_lo units: D += a_hi * b_lo
+                for (int nh = 0; nh < nsplit; ++nh) {
+                  timed_wait(&b_full[sb], pb, prof, w_b);
+                  ptx::tc_fence_after();
+                  const uint32_t b32 = b_ring32 + sb * b_unit16;
+                  uint32_t ah = a_tap32, d = tmem_buf + (uint32_t)nh * unit_rows;
+                  for (uint32_t a = 0; a < nacc; ++a, ah += sub16, d += acc_cols) {
+#pragma unroll
+                    for (uint32_t k = 0; k < 8; k += 2) ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc1, 1);
+                  }
+                  ptx::umma_commit(&b_empty[sb]);
+                  if (++sb == SB) { sb = 0; pb ^= 1u; }
+                }
               }
+              keep = 1;
             }
             ptx::umma_commit(&a_empty[sa]);
-            ++ia;
+            if (++sa == 2) { sa = 0; pa ^= 1u; }
           }
         }
         ptx::umma_commit(&t_full[buf]);
+      }
+      if (prof) {
+        atomicAdd(p.prof + 3, (unsigned long long)(clock64() - t_start));
+        atomicAdd(p.prof + 4, w_t);
+        atomicAdd(p.prof + 5, w_a);
+        atomicAdd(p.prof + 6, w_b);
       }
     }
   } else {
@@ -321,11 +379,14 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
     const int64_t plane = (int64_t)p.Ho * p.Wo;
     const int cmax = p.y_cl2 != nullptr && p.y_Cp > p.npad ? p.y_Cp : p.npad;
     uint32_t lt = 0;
+    const bool prof = p.prof != nullptr;
+    unsigned long long w_f = 0;
+    const long long t_start = prof ? clock64() : 0;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++lt) {
       const TileCoord tc = decode_tile(p, tile);
       const GClass& C = p.cls[tc.ci];
       const uint32_t buf = lt % (uint32_t)p.nbuf, tph = (lt / (uint32_t)p.nbuf) & 1u;
-      ptx::mbar_wait(&t_full[buf], tph);
+      timed_wait(&t_full[buf], tph, prof, w_f);
       ptx::tc_fence_after();
       const bool have = C.ng > 0;                 // a class no tap reaches is bias-only
       const int64_t b = tc.b;
@@ -338,48 +399,68 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
         __nv_bfloat16* cb = p.y_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
         const int64_t lo_off = plane * p.y_Cp;
         const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.buf_cols + (uint32_t)(a * p.acc_cols);
-        for (int c0 = 0; c0 < cmax; c0 += 32) {
-          uint32_t r[32], r2[32];
-          if (c0 < p.npad && have) {
-            ptx::tmem_ld_32x32(trow + (uint32_t)c0, r);
-            if (p.concat) ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
-            ptx::tmem_ld_wait();
-          }
-          float v[32];
+        // tcgen05.ld queues behind the MMAs already issued for the next tile (measured: ~5k cycles per
+        // load-then-wait round trip while the pipe is busy), so the loads of a whole group of column
+        // chunks are issued back to back and waited for once.
+        constexpr int kGroup = 4;                                // chunks (of 32 columns) per wait
+        for (int cg0 = 0; cg0 < cmax; cg0 += 32 * kGroup) {
+          uint32_t r[kGroup][32];
+          if (have) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int co = c0 + j;
-            float f = 0.f;
-            if (co < p.Cout2 && have) {
-              f = __uint_as_float(r[j]);
-              if (p.concat) f += __uint_as_float(r2[j]);
-            }
-            if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
-            v[j] = f > 0.f ? f : f * p.slope;
-          }
-          if (!ok) continue;
-          if (yb != nullptr) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (c0 + j < p.Cout2) {
-                const int64_t pos = ypos + (int64_t)(c0 + j) * p.y_cs;
-                const int64_t dst = pos + p.y_off;
-                if (p.y_lim == 0 || (dst >= 0 && dst < p.y_lim))
-                  yb[dst] = p.y_scale ? v[j] * __ldg(p.y_scale + pos) : v[j];
+            for (int g = 0; g < kGroup; ++g) {
+              const int c0 = cg0 + 32 * g;
+              if (c0 < p.npad) {
+                // concat: the two accumulator halves are summed; issue the second half into the same wait
+                ptx::tmem_ld_32x32(trow + (uint32_t)c0, r[g]);
               }
             }
+            ptx::tmem_ld_wait();
           }
-          if (cb != nullptr && c0 < p.y_Cp) {
-            __align__(16) __nv_bfloat16 hi[32];
-            __align__(16) __nv_bfloat16 lo[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) split_bf16(v[j], hi[j], lo[j]);
-            uint4* dh = reinterpret_cast<uint4*>(cb + c0);
-            uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+          for (int g = 0; g < kGroup; ++g) {
+            const int c0 = cg0 + 32 * g;
+            if (c0 >= cmax) break;
+            uint32_t r2[32];
+            if (kConcat && have && c0 < p.npad) {
+              ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
+              ptx::tmem_ld_wait();
+            }
+            float v[32];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              dh[j] = reinterpret_cast<const uint4*>(hi)[j];
-              dl[j] = reinterpret_cast<const uint4*>(lo)[j];
+            for (int j = 0; j < 32; ++j) {
+              const int co = c0 + j;
+              float f = 0.f;
+              if (co < p.Cout2 && have) {
+                f = __uint_as_float(r[g][j]);
+                if (kConcat) f += __uint_as_float(r2[j]);
+              }
+              if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
+              v[j] = f > 0.f ? f : f * p.slope;
+            }
+            if (!ok) continue;
+            if (yb != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (c0 + j < p.Cout2) {
+                  const int64_t pos = ypos + (int64_t)(c0 + j) * p.y_cs;
+                  const int64_t dst = pos + p.y_off;
+                  if (p.y_lim == 0 || (dst >= 0 && dst < p.y_lim))
+                    yb[dst] = p.y_scale ? v[j] * __ldg(p.y_scale + pos) : v[j];
+                }
+              }
+            }
+            if (cb != nullptr && c0 < p.y_Cp) {
+              __align__(16) __nv_bfloat16 hi[32];
+              __align__(16) __nv_bfloat16 lo[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) split_bf16(v[j], hi[j], lo[j]);
+              uint4* dh = reinterpret_cast<uint4*>(cb + c0);
+              uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                dh[j] = reinterpret_cast<const uint4*>(hi)[j];
+                dl[j] = reinterpret_cast<const uint4*>(lo)[j];
+              }
             }
           }
         }
@@ -388,6 +469,10 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&t_empty[buf]);
+    }
+    if (prof && warp == 2 && lane == 0) {
+      atomicAdd(p.prof + 7, (unsigned long long)(clock64() - t_start));
+      atomicAdd(p.prof + 8, w_f);
     }
   }
   ptx::tc_fence_before();
@@ -570,11 +655,12 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
             const double bytes = (double)a_slot + (double)G.ntaps * units * b_unit;
             per_tile += kblocks * fmax(G.ntaps * t_tap, bytes / kFillBytesPerCycle);
           }
-          // epilogue (overlapped only with two TMEM buffers) + per-tile bookkeeping
+          // epilogue: measured ~180 cycles per accumulator column (4 warps, one per SM sub-partition);
+          // it hides behind the next tile's MMAs only with two TMEM buffers
           const int buf_cols = round_up(nacc * acc_cols, 32);
           const bool two_bufs = buf_cols + tm_need <= 512;
-          const double epi = acc_avg * 128.0 * npad * 4.0 / 20.0;
-          per_tile += 800.0 + (two_bufs ? 0.25 : 1.0) * epi;
+          const double epi = acc_avg * (180.0 * npad + 1500.0);
+          per_tile = two_bufs ? fmax(per_tile, epi) + 800.0 : per_tile + epi + 800.0;
           total += per_tile * n;
           tiles += n;
         }
@@ -685,7 +771,8 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   const int smem = p.SA * p.a_slot + p.SB * p.b_unit + 1024;
   static int smem_attr = 0;
   if (smem > smem_attr) {
-    SE_CUDA(cudaFuncSetAttribute(cconv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_CUDA(cudaFuncSetAttribute(cconv_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_CUDA(cudaFuncSetAttribute(cconv_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     smem_attr = smem;
   }
   if (dbg & 4)
@@ -693,7 +780,27 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
             a->transposed, a->src_Cp[0], a->nsrc == 2 ? a->src_Cp[1] : 0, npad, a->kh, a->kw, a->sh, a->sw, tc.TH, tc.TW,
             tc.nacc, p.concat, p.nsplit, tc.SA, tc.SB, rows, smem, p.tmem_cols, p.nbuf, (long long)ntiles, p.ncls);
   const unsigned grid = (unsigned)(ntiles < num_sms() ? ntiles : num_sms());
-  cconv_gemm_kernel<<<grid, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
+  static const char* prof_env = getenv("SE_GEMM_PROF");      // tuning aid: synchronous, prints per-role cycle counters
+  p.prof = nullptr;
+  if (prof_env && atoi(prof_env) != 0) {
+    static unsigned long long* d_prof = nullptr;
+    if (d_prof == nullptr) SE_CUDA(cudaMalloc(&d_prof, 16 * sizeof(unsigned long long)));
+    SE_CUDA(cudaMemsetAsync(d_prof, 0, 16 * sizeof(unsigned long long), s));
+    p.prof = d_prof;
+  }
+  if (concat) cconv_gemm_kernel<true><<<grid, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
+  else cconv_gemm_kernel<false><<<grid, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
+  if (p.prof != nullptr) {
+    unsigned long long h[16];
+    SE_CUDA(cudaStreamSynchronize(s));
+    SE_CUDA(cudaMemcpy(h, p.prof, sizeof(h), cudaMemcpyDeviceToHost));
+    const double g = (double)grid, tl = (double)ntiles / g;
+    fprintf(stderr, "se_cconv_gemm prof: N=%d Cp=%d k=%dx%d tiles/cta=%.1f | per tile kcyc: producer %.1f (wait a_empty %.1f, b_empty %.1f) | "
+            "mma %.1f (wait t_empty %.1f, a_full %.1f, b_full %.1f) | epilogue %.1f (wait t_full %.1f)\n",
+            npad, a->src_Cp[0] + (a->nsrc == 2 ? a->src_Cp[1] : 0), a->kh, a->kw, tl,
+            h[0] / g / tl / 1e3, h[1] / g / tl / 1e3, h[2] / g / tl / 1e3, h[3] / g / tl / 1e3, h[4] / g / tl / 1e3,
+            h[5] / g / tl / 1e3, h[6] / g / tl / 1e3, h[7] / g / tl / 1e3, h[8] / g / tl / 1e3);
+  }
   return check_launch("cconv_gemm_kernel");
 }
 

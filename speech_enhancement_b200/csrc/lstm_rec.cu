@@ -1,0 +1,146 @@
+// Recurrent half of an LSTM layer as one persistent kernel.
+//
+// The reference runs ComplexLSTM as four nn.LSTM passes (/root/reference/models/modules/
+// complex_nn.py:115-145); on a GPU the time-step loop of each pass is a chain of ~T tiny launches /
+// grid syncs.  Here the input projection  P[n,t,:] = W_ih x[n,t] + b_ih + b_hh  is hoisted into one
+// GEMM by the caller, and this kernel walks the T steps of a few batch rows entirely on one SM:
+//   gates = P[n,t] + W_hh h_{t-1};  i,f,o = sigmoid, g = tanh (gate order i|f|g|o, torch.nn.LSTM);
+//   c_t = f c_{t-1} + i g;  h_t = o tanh(c_t)
+// Batch rows never interact, so there is no inter-CTA synchronisation at all: one thread per gate
+// column (4H = 512 threads for H = 128) keeps its W_hh row on chip for the whole sequence -- KR
+// values in registers, the other H-KR in shared memory, column-major so a warp reads consecutive
+// words -- and h_{t-1} is broadcast from shared memory.  Two __syncthreads per step.
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "common.cuh"
+#include "../../include/se_b200.h"
+
+namespace se {
+
+// full-precision libm forms: the state feeds back T times, so the fast intrinsics' few-ulp errors (and
+// the cancellation of 1 - 2/(e^2x + 1) near 0) would show up at the 1e-5 parity bar
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+__device__ __forceinline__ float tanhf_(float x) { return tanhf(x); }
+
+template <int H, int KR, int R>
+__global__ void __launch_bounds__(4 * H, 1)
+lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, float* __restrict__ h_out,
+                int64_t N, int64_t T) {
+  constexpr int G = 4 * H, KS = H - KR;
+  extern __shared__ __align__(16) float smem[];
+  float* w_s = smem;                 // [KS][G]
+  float* h_s = w_s + KS * G;         // [R][H]
+  float* g_s = h_s + R * H;          // [R][G]
+  const int j = threadIdx.x;
+  const int gate = j / H;            // warp-uniform (H is a multiple of 32)
+
+  float w[KR];
+#pragma unroll
+  for (int k = 0; k < KR; ++k) w[k] = __ldg(w_hh + (int64_t)j * H + k);
+  for (int k = 0; k < KS; ++k) w_s[k * G + j] = __ldg(w_hh + (int64_t)j * H + KR + k);
+
+  for (int64_t row0 = (int64_t)blockIdx.x * R; row0 < N; row0 += (int64_t)gridDim.x * R) {
+    float c[R];
+    const float* prow[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      c[r] = 0.f;
+      const int64_t row = row0 + r < N ? row0 + r : N - 1;       // tail rows recompute the last row (never stored)
+      prow[r] = pre + row * T * G + j;
+    }
+    for (int i = j; i < R * H; i += G) h_s[i] = 0.f;
+    float nxt[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) nxt[r] = __ldg(prow[r]);
+    __syncthreads();
+    for (int64_t t = 0; t < T; ++t) {
+      float acc[R][2];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        acc[r][0] = nxt[r];
+        acc[r][1] = 0.f;
+        if (t + 1 < T) nxt[r] = __ldg(prow[r] + (t + 1) * G);
+      }
+#pragma unroll
+      for (int k = 0; k < KR; k += 4) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const float4 hv = *reinterpret_cast<const float4*>(h_s + r * H + k);
+          acc[r][0] = fmaf(w[k], hv.x, acc[r][0]);
+          acc[r][1] = fmaf(w[k + 1], hv.y, acc[r][1]);
+          acc[r][0] = fmaf(w[k + 2], hv.z, acc[r][0]);
+          acc[r][1] = fmaf(w[k + 3], hv.w, acc[r][1]);
+        }
+      }
+#pragma unroll 4
+      for (int k = 0; k < KS; k += 4) {
+        const float w0 = w_s[(k + 0) * G + j], w1 = w_s[(k + 1) * G + j];
+        const float w2 = w_s[(k + 2) * G + j], w3 = w_s[(k + 3) * G + j];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const float4 hv = *reinterpret_cast<const float4*>(h_s + r * H + KR + k);
+          acc[r][0] = fmaf(w0, hv.x, acc[r][0]);
+          acc[r][1] = fmaf(w1, hv.y, acc[r][1]);
+          acc[r][0] = fmaf(w2, hv.z, acc[r][0]);
+          acc[r][1] = fmaf(w3, hv.w, acc[r][1]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float a = acc[r][0] + acc[r][1];
+        g_s[r * G + j] = gate == 2 ? tanhf_(a) : sigmoidf_(a);
+      }
+      __syncthreads();
+      if (j < H) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const float* g = g_s + r * G;
+          c[r] = g[H + j] * c[r] + g[j] * g[2 * H + j];
+          const float h = g[3 * H + j] * tanhf_(c[r]);
+          h_s[r * H + j] = h;
+          if (row0 + r < N) h_out[((row0 + r) * T + t) * H + j] = h;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+template <int H, int KR, int R>
+static int launch_lstm(const float* pre, const float* w_hh, float* h_out, int64_t N, int64_t T, cudaStream_t s) {
+  constexpr int G = 4 * H;
+  const int smem = ((H - KR) * G + R * H + R * G) * (int)sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    SE_CUDA(cudaFuncSetAttribute(lstm_rec_kernel<H, KR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  int64_t ctas = (N + R - 1) / R;
+  if (ctas > num_sms()) ctas = num_sms();
+  lstm_rec_kernel<H, KR, R><<<(unsigned)ctas, G, smem, s>>>(pre, w_hh, h_out, N, T);
+  return check_launch("lstm_rec_kernel");
+}
+
+}  // namespace se
+
+extern "C" int se_lstm_rec_supported(int H) { return (H == 128 || H == 64) ? 1 : 0; }
+
+extern "C" int se_lstm_rec_fwd(const float* pre_gates, const float* w_hh, int64_t N, int64_t T, int H, float* h_out,
+                               void* stream) {
+  SE_REQUIRE(pre_gates && w_hh && h_out, "se_lstm_rec_fwd: null pointer");
+  SE_REQUIRE(N >= 0 && T >= 0 && H > 0, "se_lstm_rec_fwd: bad dims");
+  if (N == 0 || T == 0) return SE_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int sms = se::num_sms();
+  if (H == 128) {
+    if (N <= sms) return se::launch_lstm<128, 64, 1>(pre_gates, w_hh, h_out, N, T, s);
+    if (N <= 2 * sms) return se::launch_lstm<128, 64, 2>(pre_gates, w_hh, h_out, N, T, s);
+    return se::launch_lstm<128, 64, 4>(pre_gates, w_hh, h_out, N, T, s);
+  }
+  if (H == 64) {
+    if (N <= sms) return se::launch_lstm<64, 64, 1>(pre_gates, w_hh, h_out, N, T, s);
+    if (N <= 2 * sms) return se::launch_lstm<64, 64, 2>(pre_gates, w_hh, h_out, N, T, s);
+    return se::launch_lstm<64, 64, 4>(pre_gates, w_hh, h_out, N, T, s);
+  }
+  return se::fail(SE_ERR_UNSUPPORTED, "se_lstm_rec_fwd: hidden size %d not supported (64 or 128)", H);
+}

@@ -118,6 +118,21 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same MMA with both shared-memory descriptors given by their low words only; the high word is the
+// constant part of a K-major SWIZZLE_128B descriptor (SBO 1024 B, version 1, layout type 2).  Lets the
+// issuing thread do all descriptor arithmetic in 32 bits.
+constexpr uint32_t kDescHiSw128 = 0x40004040u;
+__device__ __forceinline__ void umma_bf16_lo32(uint32_t tmem_d, uint32_t a_lo32, uint32_t b_lo32, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo32), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHiSw128)
+      : "memory");
+}
 // variants with operand-collector hints (the tensor core keeps A, or in .ws mode B, in its collector
 // buffer so the next MMA does not re-read it from shared memory)
 #define SE_UMMA_VARIANT(NAME, OPCODE)                                                                   \

@@ -2,13 +2,45 @@
 
 Same class names, constructor signatures, parameter/buffer names and numerics as
 /root/reference/models/modules/complex_nn.py:93-360 so reference checkpoints load and the
-caller models behave identically; they are NOT part of the accelerated path (they are the
-"next" rows of SURVEY.md 8f) and run on whatever device their input lives on.
+caller models behave identically; they are the "next" rows of SURVEY.md 8f.  ComplexLSTM inference on CUDA runs its time loop
+in csrc/lstm_rec.cu (8f rank 3); everything else here is stock PyTorch on whatever device the
+input lives on.
 """
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
+from .. import _abi
 from .complex_nn import split_complex, merge_real_imag, _halve
+
+
+def _lstm_rec_ok(lstm, x):
+    """the persistent recurrent kernel (csrc/lstm_rec.cu) serves inference on a unidirectional fp32 LSTM"""
+    return (x.is_cuda and x.dtype == torch.float32 and not lstm.bidirectional and lstm.proj_size == 0
+            and not (torch.is_grad_enabled() and (x.requires_grad or lstm.weight_hh_l0.requires_grad))
+            and not (lstm.training and lstm.dropout > 0 and lstm.num_layers > 1)
+            and _abi.lib().se_lstm_rec_supported(lstm.hidden_size) == 1)
+
+
+def lstm_forward(lstm, x):
+    """nn.LSTM forward (zero initial state, output sequence only) with the input projection as one GEMM
+    and the time loop in se_lstm_rec_fwd.  x: [N, T, in] if batch_first else [T, N, in]."""
+    if not lstm.batch_first:
+        x = x.transpose(0, 1)
+    x = x.contiguous()
+    N, T, _ = x.shape
+    H = lstm.hidden_size
+    with torch.cuda.device(x.device):
+        for layer in range(lstm.num_layers):
+            w_ih, w_hh = getattr(lstm, f'weight_ih_l{layer}'), getattr(lstm, f'weight_hh_l{layer}')
+            bias = getattr(lstm, f'bias_ih_l{layer}') + getattr(lstm, f'bias_hh_l{layer}') if lstm.bias else None
+            pre = F.linear(x, w_ih, bias)                       # [N, T, 4H], fp32 (no TF32: torch default)
+            h = torch.empty((N, T, H), device=x.device, dtype=torch.float32)
+            with _abi.stage('lstm'):
+                _abi.check(_abi.lib().se_lstm_rec_fwd(_abi.ptr(pre), _abi.ptr(w_hh.contiguous()), N, T, H,
+                                                      _abi.ptr(h), _abi.stream_ptr()))
+            x = h
+    return x if lstm.batch_first else x.transpose(0, 1)
 
 
 class ComplexLinear(nn.Module):
@@ -40,13 +72,18 @@ class ComplexLSTM(nn.Module):
         # both inputs share each LSTM's weights: run them stacked on the batch axis (2 calls, not 4)
         bdim = 0 if self.real_lstm.batch_first else 1
         both = torch.cat([real, imag], dim=bdim)
-        # cuDNN RNNs default to TF32 math on CUDA; the parity target is the fp32 reference
-        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
-            by_real, _ = self.real_lstm(both)
-            by_imag, _ = self.imag_lstm(both)
+        if self.rec_kernel and _lstm_rec_ok(self.real_lstm, both):
+            by_real, by_imag = lstm_forward(self.real_lstm, both), lstm_forward(self.imag_lstm, both)
+        else:
+            # cuDNN RNNs default to TF32 math on CUDA; the parity target is the fp32 reference
+            with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+                by_real, _ = self.real_lstm(both)
+                by_imag, _ = self.imag_lstm(both)
         r2r, i2r = torch.chunk(by_real, 2, dim=bdim)
         r2i, i2i = torch.chunk(by_imag, 2, dim=bdim)
         return merge_real_imag(x, r2r - i2i, r2i + i2r, dim=-1)
+
+    rec_kernel = True       # class switch: False forces the stock cuDNN path
 
     def flatten_parameters(self):
         self.real_lstm.flatten_parameters()
