@@ -283,7 +283,10 @@ def run_ours(args):
     stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / args.steps)
     roofline = {'bound': 'tensor', 'kernel': 'complex conv stack (12 se_cconv*_fwd launches per step)',
                 'achieved': tflops, 'peak': pk['bf16_tflops_sustained'], 'unit': 'TFLOP/s',
-                'frac': tflops / pk['bf16_tflops_sustained'], 'traffic': None,
+                'frac': tflops / pk['bf16_tflops_sustained'],
+                # dram__bytes_read + write summed over the 11 conv GEMM launches of one step, from the ncu --set full
+                # capture profiles/r1c_gemm_full_summary.txt (B=64: 25.46 GB), scaled per utterance
+                'traffic': 25.458e9 / 64 * B, 'traffic_unit': 'B per step (all conv GEMM launches)',
                 'peak_source': pk['source'] + ' bf16 dense (sustained)',
                 'note': 'algorithmic FLOPs (65.95 GFLOP/utt); the tensor engine issues 3 bf16 passes per product'}
 
@@ -308,7 +311,7 @@ def main():
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
-    ap.add_argument('--batch', type=int, default=int(os.environ.get('SE_BENCH_BATCH', '16')),
+    ap.add_argument('--batch', type=int, default=int(os.environ.get('SE_BENCH_BATCH', '64')),
                     help='4 s utterances per GPU per step')
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     args = ap.parse_args()
