@@ -60,6 +60,7 @@ struct GemmParams {
   __nv_bfloat16* y_cl2;
   int64_t y_bs, y_cs, y_hs, y_ws, y_off, y_lim;   // fp32 output addressing (defaults = NCHW)
   const float* y_scale;                           // optional per-position scale (iSTFT normaliser)
+  int y_vec4;                                     // fp32 output rows are channel-contiguous and 16-byte aligned
   unsigned long long* prof;                       // SE_GEMM_PROF=1: per-role wait/work cycle counters (tuning aid)
 };
 
@@ -158,6 +159,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
   return d;
 }
 
+constexpr int kGemmThreads = 320;          // warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 epilogue
+
 struct TileCoord { int ci, b, h0, w0, nacc; };
 
 // mbarrier wait that charges its duration to `acc` when profiling is on
@@ -190,12 +193,13 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmParams& p, int tile) 
 // ahead across tile boundaries, and with two TMEM accumulator buffers (when nacc * acc_cols <= 256)
 // the epilogue of tile i overlaps the MMAs of tile i+1.
 template <bool kConcat>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kGemmThreads, 1)
 cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                   const __grid_constant__ CUtensorMap tmW, const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t a_full[2], a_empty[2], b_full[8], b_empty[8], t_full[2], t_empty[2];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ __align__(16) float s_bias[320];          // folded bias per accumulator column, 0 beyond Cout2
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -208,9 +212,10 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
     ptx::prefetch_tmap(&tmW);
     for (int s = 0; s < p.SA; ++s) { ptx::mbar_init(&a_full[s], 1); ptx::mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < p.SB; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&t_full[s], 1); ptx::mbar_init(&t_empty[s], 4); }
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&t_full[s], 1); ptx::mbar_init(&t_empty[s], 8); }
     ptx::fence_mbar_init();
   }
+  for (int c = threadIdx.x; c < 320; c += blockDim.x) s_bias[c] = (c < p.Cout2 && p.bias != nullptr) ? __ldg(p.bias + c) : 0.f;
   if (warp == 1) {
     ptx::tmem_alloc(&tmem_base_slot, (uint32_t)p.tmem_cols);
     ptx::tmem_relinquish();
@@ -372,12 +377,21 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
       }
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> (+bias, activation) -> NCHW fp32 and/or CL2 bf16 =====
+    // ===== epilogue: TMEM -> registers -> (+bias, activation) -> fp32 and/or CL2 bf16 =====
+    // Eight warps: warp w may only touch TMEM lanes 32*(w%4)..+31, so two warps share each lane
+    // quarter and take alternate 32-column chunks.  All per-element decisions (which outputs, limits,
+    // scale, vector stores) are warp-uniform and hoisted out of the column loops.
     const int q = warp & 3;                       // TMEM lane quarter this warp may access
+    const int chalf = (warp - 2) >> 2;            // 0: even chunks, 1: odd chunks
     const int m = q * 32 + lane;
     const int hl = m / p.TW, wl = m - hl * p.TW;
     const int64_t plane = (int64_t)p.Ho * p.Wo;
     const int cmax = p.y_cl2 != nullptr && p.y_Cp > p.npad ? p.y_Cp : p.npad;
+    const bool do_f32 = p.y != nullptr, do_cl2 = p.y_cl2 != nullptr;
+    const bool checked = p.y_lim != 0 || p.y_scale != nullptr;
+    const bool act = p.slope != 1.f;
+    const float slope = p.slope;
+    const int64_t lo_off = plane * p.y_Cp;
     uint32_t lt = 0;
     const bool prof = p.prof != nullptr;
     unsigned long long w_f = 0;
@@ -394,73 +408,85 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
         const int qh = tc.h0 + a * p.TH + hl, qw = tc.w0 + wl;
         const int ho = qh * C.oh_mul + C.oh_add, wo = qw * C.ow_mul + C.ow_add;
         const bool ok = qh < C.Hq_out && qw < C.Wq_out && ho < p.Ho && wo < p.Wo;
-        float* yb = p.y ? p.y + b * p.y_bs + (int64_t)ho * p.y_hs : nullptr;
         const int64_t ypos = (int64_t)wo * p.y_ws;           // + co * y_cs: position inside the (b, ho) row block
-        __nv_bfloat16* cb = p.y_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
-        const int64_t lo_off = plane * p.y_Cp;
+        float* yb = do_f32 ? p.y + b * p.y_bs + (int64_t)ho * p.y_hs + p.y_off + ypos : nullptr;
+        __nv_bfloat16* cb = do_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
         const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.buf_cols + (uint32_t)(a * p.acc_cols);
-        // tcgen05.ld queues behind the MMAs already issued for the next tile (measured: ~5k cycles per
-        // load-then-wait round trip while the pipe is busy), so the loads of a whole group of column
-        // chunks are issued back to back and waited for once.
-        constexpr int kGroup = 4;                                // chunks (of 32 columns) per wait
-        for (int cg0 = 0; cg0 < cmax; cg0 += 32 * kGroup) {
-          uint32_t r[kGroup][32];
-          if (have) {
-#pragma unroll
-            for (int g = 0; g < kGroup; ++g) {
-              const int c0 = cg0 + 32 * g;
-              if (c0 < p.npad) {
-                // concat: the two accumulator halves are summed; issue the second half into the same wait
-                ptx::tmem_ld_32x32(trow + (uint32_t)c0, r[g]);
-              }
-            }
-            ptx::tmem_ld_wait();
-          }
-#pragma unroll
-          for (int g = 0; g < kGroup; ++g) {
-            const int c0 = cg0 + 32 * g;
-            if (c0 >= cmax) break;
-            uint32_t r2[32];
-            if (kConcat && have && c0 < p.npad) {
+        for (int c0 = chalf * 32; c0 < cmax; c0 += 64) {
+          float v[32];
+          if (have && c0 < p.npad) {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(trow + (uint32_t)c0, r);
+            if (kConcat) {
+              uint32_t r2[32];
               ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
               ptx::tmem_ld_wait();
-            }
-            float v[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int co = c0 + j;
-              float f = 0.f;
-              if (co < p.Cout2 && have) {
-                f = __uint_as_float(r[g][j]);
-                if (kConcat) f += __uint_as_float(r2[j]);
-              }
-              if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
-              v[j] = f > 0.f ? f : f * p.slope;
+              for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]);
+            } else {
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
             }
-            if (!ok) continue;
-            if (yb != nullptr) {
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0.f;
+          }
+          if (!ok) continue;
+          {
+            const float4* b4 = reinterpret_cast<const float4*>(s_bias + c0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 bb = b4[j];
+              v[4 * j] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
+            }
+          }
+          if (act) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f) + slope * fminf(v[j], 0.f);
+          }
+          if (do_f32 && c0 < p.Cout2) {
+            const int nv = p.Cout2 - c0;                      // valid columns in this chunk (may exceed 32)
+            if (p.y_vec4) {
+              float4* y4 = reinterpret_cast<float4*>(yb + c0);
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (4 * j + 3 < nv) y4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            } else if (!checked) {
+              float* yp = yb + (int64_t)c0 * p.y_cs;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nv) yp[(int64_t)j * p.y_cs] = v[j];
+            } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
-                if (c0 + j < p.Cout2) {
+                if (j < nv) {
                   const int64_t pos = ypos + (int64_t)(c0 + j) * p.y_cs;
                   const int64_t dst = pos + p.y_off;
                   if (p.y_lim == 0 || (dst >= 0 && dst < p.y_lim))
-                    yb[dst] = p.y_scale ? v[j] * __ldg(p.y_scale + pos) : v[j];
+                    yb[(int64_t)(c0 + j) * p.y_cs] = p.y_scale ? v[j] * __ldg(p.y_scale + pos) : v[j];
                 }
               }
             }
-            if (cb != nullptr && c0 < p.y_Cp) {
-              __align__(16) __nv_bfloat16 hi[32];
-              __align__(16) __nv_bfloat16 lo[32];
+          }
+          if (do_cl2 && c0 < p.y_Cp) {
+            uint32_t hi[16], lo[16];
 #pragma unroll
-              for (int j = 0; j < 32; ++j) split_bf16(v[j], hi[j], lo[j]);
-              uint4* dh = reinterpret_cast<uint4*>(cb + c0);
-              uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+            for (int j = 0; j < 16; ++j) {
+              const float f0 = v[2 * j], f1 = v[2 * j + 1];
+              const __nv_bfloat162 h2 = __floats2bfloat162_rn(f0, f1);
+              const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h2);
+              const float r0 = f0 - __uint_as_float(hb << 16), r1 = f1 - __uint_as_float(hb & 0xffff0000u);
+              const __nv_bfloat162 l2 = __floats2bfloat162_rn(r0, r1);
+              hi[j] = hb;
+              lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
+            }
+            uint4* dh = reinterpret_cast<uint4*>(cb + c0);
+            uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                dh[j] = reinterpret_cast<const uint4*>(hi)[j];
-                dl[j] = reinterpret_cast<const uint4*>(lo)[j];
-              }
+            for (int j = 0; j < 4; ++j) {
+              dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+              dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
             }
           }
         }
@@ -731,6 +757,9 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     p.y_bs = (int64_t)a->Cout2 * plane; p.y_cs = plane; p.y_hs = a->Wo; p.y_ws = 1; p.y_off = 0; p.y_lim = 0;
   }
   p.y_scale = a->y_scale;
+  p.y_vec4 = (p.y != nullptr && p.y_cs == 1 && p.y_lim == 0 && p.y_scale == nullptr && a->Cout2 % 4 == 0 &&
+              p.y_bs % 4 == 0 && p.y_hs % 4 == 0 && p.y_ws % 4 == 0 && p.y_off % 4 == 0 &&
+              reinterpret_cast<uintptr_t>(p.y) % 16 == 0) ? 1 : 0;
   p.kblocks[0] = a->src_Cp[0] / 64; p.kcol0[0] = 0;
   p.kblocks[1] = a->nsrc == 2 ? a->src_Cp[1] / 64 : 0; p.kcol0[1] = a->src_Cp[0];
   int64_t ntiles = 0;
@@ -788,8 +817,8 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     SE_CUDA(cudaMemsetAsync(d_prof, 0, 16 * sizeof(unsigned long long), s));
     p.prof = d_prof;
   }
-  if (concat) cconv_gemm_kernel<true><<<grid, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
-  else cconv_gemm_kernel<false><<<grid, 192, smem, s>>>(tmX[0], tmX[1], tmW, p);
+  if (concat) cconv_gemm_kernel<true><<<grid, kGemmThreads, smem, s>>>(tmX[0], tmX[1], tmW, p);
+  else cconv_gemm_kernel<false><<<grid, kGemmThreads, smem, s>>>(tmX[0], tmX[1], tmW, p);
   if (p.prof != nullptr) {
     unsigned long long h[16];
     SE_CUDA(cudaStreamSynchronize(s));
