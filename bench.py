@@ -264,7 +264,7 @@ def run_ours(args):
         step(i)
     tot = st.totals_ms()
     st.close()
-    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm'):
+    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm', 'linear'):
         tot.setdefault(k, 0.0)
     T = (L + 512 - 400) // 100 + 1
     Lp = out_len or (T - 1) * 100 + 400 - 512
@@ -279,6 +279,7 @@ def run_ours(args):
     stages['cconv'] = {'ms': t_conv * 1e3, 'TFLOP/s': tflops, 'launches': len(st.events.get('cconv', [])) // nprof}
     stages['cl2_convert_ms'] = tot['cl2'] / nprof
     stages['lstm_recurrence_ms'] = tot['lstm'] / nprof
+    stages['lstm_linear_projections_ms'] = tot['linear'] / nprof
     stages['step_ms'] = ms / args.steps
     stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / args.steps)
     roofline = {'bound': 'tensor', 'kernel': 'complex conv stack (12 se_cconv*_fwd launches per step)',

@@ -138,6 +138,10 @@ SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void
 /* fp32 x[b*xs_b + c*xs_c + h*xs_h + w] -> CL2 (same as se_cl2_from_nchw for arbitrary outer strides). */
 SE_API int se_cl2_from_strided(const float* x, int64_t xs_b, int64_t xs_c, int64_t xs_h, int64_t B, int C, int H,
                         int W, void* cl2, int Cp, void* stream);
+/* row-major fp32 x[M][ld] (first K columns) -> CL2 image of M pixels x K channels (one image row);
+ * with se_cconv_gemm (1x1 kernel, y_cs = 1) this is a bf16x3 linear layer y = x W^T + b
+ * (nn.Linear / the LSTM input projections of complex_nn.py:93-145).                              */
+SE_API int se_cl2_from_rows(const float* x, int64_t M, int K, int64_t ld, void* cl2, int Cp, void* stream);
 /* STFT framing for the tensor-core path (replaces the F.pad(reflect) + strided conv1d unfolding of
  * /root/reference/models/conv_stft.py:60-63): cl2[s][b][q][col] = reflect_pad(x)[b][q*hop + col],
  * bf16 hi|lo planes, col < hop (zero above), q < Q.  One image row per utterance.              */
@@ -174,11 +178,11 @@ SE_API int se_polar_to_rect(const float* mags, const float* phase, int64_t B, in
 
 /* ---- recurrent half of an LSTM layer (replaces the time-step loop of the four
  * nn.LSTM passes of /root/reference/models/modules/complex_nn.py:131-142) -------------------------
- * pre_gates [N][T][4H] = W_ih x + b_ih + b_hh (gate order i|f|g|o), w_hh [4H][H], zero initial state;
+ * pre_gates [N][T][pre_ld >= 4H] = W_ih x + b_ih + b_hh (gate order i|f|g|o), w_hh [4H][H], zero state;
  * writes h_out [N][T][H].  One persistent CTA per batch row(s), no inter-CTA synchronisation.     */
 SE_API int se_lstm_rec_supported(int H);
-SE_API int se_lstm_rec_fwd(const float* pre_gates, const float* w_hh, int64_t N, int64_t T, int H, float* h_out,
-                           void* stream);
+SE_API int se_lstm_rec_fwd(const float* pre_gates, int64_t pre_ld, const float* w_hh, int64_t N, int64_t T, int H,
+                           float* h_out, void* stream);
 
 #ifdef __cplusplus
 }

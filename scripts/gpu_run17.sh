@@ -1,9 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r19_tests.log 2>&1
-echo "tests rc=$?"; tail -5 gpurun_out/r19_tests.log
-SE_GEMM_PROF=1 timeout 600 python bench.py --steps 1 --warmup 3 > gpurun_out/r19_prof.log 2>&1
-grep "se_cconv_gemm prof" gpurun_out/r19_prof.log | tail -15
-timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/r19_bench.log 2>&1; tail -1 gpurun_out/r19_bench.log | python -c "
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r20_tests.log 2>&1
+echo "tests rc=$?"; tail -5 gpurun_out/r20_tests.log
+SE_GEMM_PROF=1 timeout 600 python bench.py --steps 1 --warmup 3 > gpurun_out/r20_prof.log 2>&1
+grep "se_cconv_gemm prof" gpurun_out/r20_prof.log | tail -15
+timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/r20_bench.log 2>&1; tail -1 gpurun_out/r20_bench.log | python -c "
 import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['stages'])"
 timeout 300 python scripts/stft_bench.py 2>&1 | tail -2

@@ -43,7 +43,8 @@ _SIGS = {
     'se_cconv_small_cin': (C.c_int, [_P, _L, _L, _L, _L, _I, _I, _I, _I, _I, _P, _P, C.c_float] + [_I] * 7
                            + [_P, _P, _I, _I, _I, _P]),
     'se_lstm_rec_supported': (C.c_int, [_I]),
-    'se_lstm_rec_fwd': (C.c_int, [_P, _P, _L, _L, _I, _P, _P]),
+    'se_lstm_rec_fwd': (C.c_int, [_P, _L, _P, _L, _L, _I, _P, _P]),
+    'se_cl2_from_rows': (C.c_int, [_P, _L, _I, _L, _P, _I, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),
 }

@@ -239,3 +239,80 @@ class FusedBlock:
                 self.pw, _abi.ptr(y), _abi.ptr(y_act.data) if y_act is not None else None,
                 y_act.Cp if y_act is not None else 0, Ho, Wo, _abi.stream_ptr()))
         return y_act, y
+
+
+class LinearOperand:
+    """y = x W^T + b on the bf16x3 GEMM engine for one or several stacked nn.Linear-style weights
+    (the LSTM input projections and ComplexLinear of /root/reference/models/modules/complex_nn.py:93-145).
+
+    `parts` is a callable returning [(weight [N_i, K], bias [N_i] | None | tuple of biases to sum), ...];
+    the operand (weights split into bf16 hi|lo, <= 256 output columns per launch) is rebuilt whenever one
+    of the tensors changes.  x may be a column slice of a wider row-major matrix (row stride `ld`).
+    """
+
+    def __init__(self, parts):
+        self._parts = parts
+        self._key = None
+        self._ops = None
+
+    def _operands(self):
+        parts = self._parts()
+        flat = []
+        for w, b in parts:
+            flat.append(w)
+            flat.extend(b if isinstance(b, (tuple, list)) else [b])
+        key = tuple((t.data_ptr(), t._version, t.device) if t is not None else None for t in flat)
+        if key != self._key:
+            with torch.no_grad():
+                ws, bs = [], []
+                for w, b in parts:
+                    ws.append(w.detach().float())
+                    if isinstance(b, (tuple, list)):
+                        b = sum(t.detach().float() for t in b if t is not None) if any(t is not None for t in b) else None
+                    bs.append(b.detach().float() if b is not None else torch.zeros(w.shape[0], device=w.device))
+                W = torch.cat(ws, 0).contiguous()
+                bias = torch.cat(bs, 0).contiguous()
+                N, K = W.shape
+                Cp = _cp(K)
+                chunks = []
+                lib = _abi.lib()
+                with torch.cuda.device(W.device):
+                    for c0 in range(0, N, 256):
+                        n = min(256, N - c0)
+                        wq = torch.empty(lib.se_cconv_wq_elems(n, Cp, 1), device=W.device, dtype=torch.bfloat16)
+                        _abi.check(lib.se_cconv_prep_weight(_abi.ptr(W[c0:c0 + n]), n, K, 1, None, Cp, _abi.ptr(wq),
+                                                            _abi.stream_ptr()))
+                        chunks.append((c0, n, wq))
+            self._ops = dict(N=N, K=K, Cp=Cp, chunks=chunks, bias=bias, W=W)
+            self._key = key
+        return self._ops
+
+    def __call__(self, x, out=None, out_col=0):
+        """x: [M, K] fp32 CUDA with unit column stride (row stride free).  Writes columns
+        [out_col, out_col + N) of `out` ([M, >= out_col + N] fp32 contiguous; allocated when None)."""
+        ops = self._operands()
+        M, K = x.shape
+        N, Cp = ops['N'], ops['Cp']
+        if K != ops['K'] or x.stride(1) != 1 or x.dtype != torch.float32 or not x.is_cuda:
+            raise RuntimeError(f'LinearOperand: expected fp32 CUDA [M, {ops["K"]}] with unit column stride')
+        if out is None:
+            out = torch.empty((M, N), device=x.device, dtype=torch.float32)
+        ldo = out.stride(0)
+        if M == 0:
+            return out
+        H, W = (2, M // 2) if M % 2 == 0 else (1, M)       # two image rows let two accumulators share a weight unit
+        lib = _abi.lib()
+        with torch.cuda.device(x.device), _abi.stage('linear'):
+            img = torch.empty((1, 2, H, W, Cp), device=x.device, dtype=torch.bfloat16)
+            _abi.check(lib.se_cl2_from_rows(_abi.ptr(x), M, K, x.stride(0), _abi.ptr(img), Cp, _abi.stream_ptr()))
+            for c0, n, wq in ops['chunks']:
+                a = _abi.ConvArgs()
+                a.transposed, a.B, a.nsrc = 0, 1, 1
+                a.src[0] = img.data_ptr()
+                a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, H, W
+                a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.Ho, a.Wo = H, W, n, 1, 1, 1, 1, H, W
+                a.wq, a.bias, a.slope = wq.data_ptr(), ops['bias'].data_ptr() + 4 * c0, 1.0
+                a.y_nchw = out.data_ptr() + 4 * (out_col + c0)
+                a.y_cs, a.y_ws, a.y_hs = 1, ldo, W * ldo
+                _abi.check(lib.se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+        return out

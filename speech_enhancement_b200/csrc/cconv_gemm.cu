@@ -961,6 +961,38 @@ stft_frames_cl2_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ 
 }
 }  // namespace se
 
+// Row-major fp32 matrix x[M][ld] (K <= ld columns used) -> CL2 image with one pixel per row:
+// cl2[s][m][col] (col < K, zero above).  Feeds plain linear layers (LSTM input projections,
+// ComplexLinear: /root/reference/models/modules/complex_nn.py:93-145) to the GEMM engine.
+namespace se {
+__global__ void __launch_bounds__(256)
+cl2_from_rows_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t M, int K, int64_t ld, int Cp) {
+  const int vec = Cp / 8;
+  const int64_t total = M * vec, plane = M * (int64_t)Cp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int v8 = (int)(i % vec);
+    const int64_t m = i / vec;
+    const float* xr = x + m * ld + v8 * 8;
+    __align__(16) __nv_bfloat16 hi[8], lo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) split_bf16(v8 * 8 + j < K ? __ldg(xr + j) : 0.f, hi[j], lo[j]);
+    const int64_t off = m * Cp + v8 * 8;
+    *reinterpret_cast<uint4*>(out + off) = *reinterpret_cast<const uint4*>(hi);
+    *reinterpret_cast<uint4*>(out + plane + off) = *reinterpret_cast<const uint4*>(lo);
+  }
+}
+}  // namespace se
+
+extern "C" int se_cl2_from_rows(const float* x, int64_t M, int K, int64_t ld, void* cl2, int Cp, void* stream) {
+  SE_REQUIRE(x && cl2, "se_cl2_from_rows: null pointer");
+  SE_REQUIRE(M >= 0 && K > 0 && ld >= K && Cp >= K && Cp % 64 == 0, "se_cl2_from_rows: bad dims");
+  if (M == 0) return SE_OK;
+  const int64_t total = M * (Cp / 8);
+  const unsigned blocks = (unsigned)std::min<int64_t>((total + 255) / 256, 148 * 16);
+  se::cl2_from_rows_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<__nv_bfloat16*>(cl2), M, K, ld, Cp);
+  return se::check_launch("se_cl2_from_rows");
+}
+
 extern "C" int se_stft_frames_cl2(const float* x, int64_t B, int64_t L, int hop, int pad, int Q, int Cp, void* cl2,
                                   void* stream) {
   SE_REQUIRE(x && cl2, "se_stft_frames_cl2: null pointer");

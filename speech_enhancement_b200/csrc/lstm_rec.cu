@@ -25,7 +25,7 @@ __device__ __forceinline__ float tanhf_(float x) { return tanhf(x); }
 template <int H, int KR, int R>
 __global__ void __launch_bounds__(4 * H, 1)
 lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, float* __restrict__ h_out,
-                int64_t N, int64_t T) {
+                int64_t N, int64_t T, int64_t pre_ld) {
   constexpr int G = 4 * H, KS = H - KR;
   extern __shared__ __align__(16) float smem[];
   float* w_s = smem;                 // [KS][G]
@@ -46,7 +46,7 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, f
     for (int r = 0; r < R; ++r) {
       c[r] = 0.f;
       const int64_t row = row0 + r < N ? row0 + r : N - 1;       // tail rows recompute the last row (never stored)
-      prow[r] = pre + row * T * G + j;
+      prow[r] = pre + row * T * pre_ld + j;
     }
     for (int i = j; i < R * H; i += G) h_s[i] = 0.f;
     float nxt[R];
@@ -59,7 +59,7 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, f
       for (int r = 0; r < R; ++r) {
         acc[r][0] = nxt[r];
         acc[r][1] = 0.f;
-        if (t + 1 < T) nxt[r] = __ldg(prow[r] + (t + 1) * G);
+        if (t + 1 < T) nxt[r] = __ldg(prow[r] + (t + 1) * pre_ld);
       }
 #pragma unroll
       for (int k = 0; k < KR; k += 4) {
@@ -107,7 +107,8 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, f
 }
 
 template <int H, int KR, int R>
-static int launch_lstm(const float* pre, const float* w_hh, float* h_out, int64_t N, int64_t T, cudaStream_t s) {
+static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh, float* h_out, int64_t N, int64_t T,
+                       cudaStream_t s) {
   constexpr int G = 4 * H;
   const int smem = ((H - KR) * G + R * H + R * G) * (int)sizeof(float);
   static bool attr_set = false;
@@ -117,7 +118,7 @@ static int launch_lstm(const float* pre, const float* w_hh, float* h_out, int64_
   }
   int64_t ctas = (N + R - 1) / R;
   if (ctas > num_sms()) ctas = num_sms();
-  lstm_rec_kernel<H, KR, R><<<(unsigned)ctas, G, smem, s>>>(pre, w_hh, h_out, N, T);
+  lstm_rec_kernel<H, KR, R><<<(unsigned)ctas, G, smem, s>>>(pre, w_hh, h_out, N, T, pre_ld);
   return check_launch("lstm_rec_kernel");
 }
 
@@ -125,22 +126,22 @@ static int launch_lstm(const float* pre, const float* w_hh, float* h_out, int64_
 
 extern "C" int se_lstm_rec_supported(int H) { return (H == 128 || H == 64) ? 1 : 0; }
 
-extern "C" int se_lstm_rec_fwd(const float* pre_gates, const float* w_hh, int64_t N, int64_t T, int H, float* h_out,
-                               void* stream) {
+extern "C" int se_lstm_rec_fwd(const float* pre_gates, int64_t pre_ld, const float* w_hh, int64_t N, int64_t T, int H,
+                               float* h_out, void* stream) {
   SE_REQUIRE(pre_gates && w_hh && h_out, "se_lstm_rec_fwd: null pointer");
-  SE_REQUIRE(N >= 0 && T >= 0 && H > 0, "se_lstm_rec_fwd: bad dims");
+  SE_REQUIRE(N >= 0 && T >= 0 && H > 0 && pre_ld >= 4 * (int64_t)H, "se_lstm_rec_fwd: bad dims");
   if (N == 0 || T == 0) return SE_OK;
   cudaStream_t s = (cudaStream_t)stream;
   const int sms = se::num_sms();
   if (H == 128) {
-    if (N <= sms) return se::launch_lstm<128, 64, 1>(pre_gates, w_hh, h_out, N, T, s);
-    if (N <= 2 * sms) return se::launch_lstm<128, 64, 2>(pre_gates, w_hh, h_out, N, T, s);
-    return se::launch_lstm<128, 64, 4>(pre_gates, w_hh, h_out, N, T, s);
+    if (N <= sms) return se::launch_lstm<128, 64, 1>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
+    if (N <= 2 * sms) return se::launch_lstm<128, 64, 2>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
+    return se::launch_lstm<128, 64, 4>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
   }
   if (H == 64) {
-    if (N <= sms) return se::launch_lstm<64, 64, 1>(pre_gates, w_hh, h_out, N, T, s);
-    if (N <= 2 * sms) return se::launch_lstm<64, 64, 2>(pre_gates, w_hh, h_out, N, T, s);
-    return se::launch_lstm<64, 64, 4>(pre_gates, w_hh, h_out, N, T, s);
+    if (N <= sms) return se::launch_lstm<64, 64, 1>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
+    if (N <= 2 * sms) return se::launch_lstm<64, 64, 2>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
+    return se::launch_lstm<64, 64, 4>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
   }
   return se::fail(SE_ERR_UNSUPPORTED, "se_lstm_rec_fwd: hidden size %d not supported (64 or 128)", H);
 }

@@ -22,25 +22,57 @@ def _lstm_rec_ok(lstm, x):
             and _abi.lib().se_lstm_rec_supported(lstm.hidden_size) == 1)
 
 
-def lstm_forward(lstm, x):
-    """nn.LSTM forward (zero initial state, output sequence only) with the input projection as one GEMM
-    and the time loop in se_lstm_rec_fwd.  x: [N, T, in] if batch_first else [T, N, in]."""
-    if not lstm.batch_first:
-        x = x.transpose(0, 1)
-    x = x.contiguous()
+def _lstm_layer_params(lstm, layer):
+    g = lambda n: getattr(lstm, f'{n}_l{layer}')
+    bias = (g('bias_ih'), g('bias_hh')) if lstm.bias else None
+    return g('weight_ih'), g('weight_hh'), bias
+
+
+def _lstm_rec(pre, col0, w_hh, N, T, H):
+    """time loop of one LSTM layer over pre-gates pre[N*T, ld] (columns col0 .. col0+4H)."""
+    h = torch.empty((N, T, H), device=pre.device, dtype=torch.float32)
+    with _abi.stage('lstm'):
+        _abi.check(_abi.lib().se_lstm_rec_fwd(pre.data_ptr() + 4 * col0, pre.stride(0), _abi.ptr(w_hh.contiguous()),
+                                              N, T, H, _abi.ptr(h), _abi.stream_ptr()))
+    return h
+
+
+def lstm_pair_forward(owner, lstms, x, engine):
+    """Several nn.LSTMs (same shape, zero initial state, output sequence only) over the SAME input
+    x [N, T, in] (batch-first, contiguous): the layer-0 input projections of all of them are one
+    GEMM, each time loop runs in se_lstm_rec_fwd.  engine 'umma' puts the projections on the bf16x3
+    tensor-core GEMM, 'torch' leaves them to fp32 F.linear."""
+    from ..chain import LinearOperand
     N, T, _ = x.shape
-    H = lstm.hidden_size
+    H, L = lstms[0].hidden_size, lstms[0].num_layers
+    cache = owner.__dict__.setdefault('_proj_ops', {})
+    outs = []
     with torch.cuda.device(x.device):
-        for layer in range(lstm.num_layers):
-            w_ih, w_hh = getattr(lstm, f'weight_ih_l{layer}'), getattr(lstm, f'weight_hh_l{layer}')
-            bias = getattr(lstm, f'bias_ih_l{layer}') + getattr(lstm, f'bias_hh_l{layer}') if lstm.bias else None
-            pre = F.linear(x, w_ih, bias)                       # [N, T, 4H], fp32 (no TF32: torch default)
-            h = torch.empty((N, T, H), device=x.device, dtype=torch.float32)
-            with _abi.stage('lstm'):
-                _abi.check(_abi.lib().se_lstm_rec_fwd(_abi.ptr(pre), _abi.ptr(w_hh.contiguous()), N, T, H,
-                                                      _abi.ptr(h), _abi.stream_ptr()))
-            x = h
-    return x if lstm.batch_first else x.transpose(0, 1)
+        x2 = x.reshape(N * T, -1)
+        if engine == 'umma':
+            op = cache.get('l0')
+            if op is None:
+                op = cache['l0'] = LinearOperand(lambda: [(_lstm_layer_params(m, 0)[0], _lstm_layer_params(m, 0)[2])
+                                                          for m in lstms])
+            pre = op(x2)                                               # [N*T, len(lstms) * 4H]
+        else:
+            pre = torch.cat([F.linear(x2, _lstm_layer_params(m, 0)[0],
+                                      sum(_lstm_layer_params(m, 0)[2]) if m.bias else None) for m in lstms], 1)
+        for i, m in enumerate(lstms):
+            h = _lstm_rec(pre, i * 4 * H, _lstm_layer_params(m, 0)[1], N, T, H)
+            for layer in range(1, L):
+                w_ih, w_hh, bias = _lstm_layer_params(m, layer)
+                if engine == 'umma':
+                    op = cache.get((i, layer))
+                    if op is None:
+                        op = cache[(i, layer)] = LinearOperand(
+                            lambda m=m, layer=layer: [(_lstm_layer_params(m, layer)[0], _lstm_layer_params(m, layer)[2])])
+                    pl = op(h.reshape(N * T, H))
+                else:
+                    pl = F.linear(h.reshape(N * T, H), w_ih, sum(bias) if bias else None)
+                h = _lstm_rec(pl, 0, w_hh, N, T, H)
+            outs.append(h)
+    return outs
 
 
 class ComplexLinear(nn.Module):
@@ -52,7 +84,24 @@ class ComplexLinear(nn.Module):
         self.real_linear = nn.Linear(ci, co, **kwargs)
         self.imag_linear = nn.Linear(ci, co, **kwargs)
 
+    engine = 'umma'         # 'umma': bf16x3 tensor-core GEMM for CUDA fp32 inference; 'torch': nn.Linear
+
     def forward(self, x):
+        if (self.engine == 'umma' and torch.is_tensor(x) and x.is_cuda and x.dtype == torch.float32 and x.dim() >= 2
+                and not (torch.is_grad_enabled() and (x.requires_grad or self.real_linear.weight.requires_grad))):
+            from ..chain import LinearOperand
+            ops = self.__dict__.setdefault('_tc_ops', None)
+            if ops is None:
+                ops = self.__dict__['_tc_ops'] = tuple(
+                    LinearOperand(lambda lin=lin: [(lin.weight, lin.bias)]) for lin in (self.real_linear, self.imag_linear))
+            K, No = self.real_linear.in_features, self.real_linear.out_features
+            x2 = x.reshape(-1, 2 * K)
+            if x2.stride(1) != 1:
+                x2 = x2.contiguous()
+            out = torch.empty((x2.shape[0], 2 * No), device=x.device, dtype=torch.float32)
+            ops[0](x2[:, :K], out=out, out_col=0)
+            ops[1](x2[:, K:], out=out, out_col=No)
+            return out.reshape(*x.shape[:-1], 2 * No)
         real, imag = split_complex(x, dim=-1)
         return merge_real_imag(x, self.real_linear(real), self.imag_linear(imag), dim=-1)
 
@@ -73,7 +122,11 @@ class ComplexLSTM(nn.Module):
         bdim = 0 if self.real_lstm.batch_first else 1
         both = torch.cat([real, imag], dim=bdim)
         if self.rec_kernel and _lstm_rec_ok(self.real_lstm, both):
-            by_real, by_imag = lstm_forward(self.real_lstm, both), lstm_forward(self.imag_lstm, both)
+            bf = self.real_lstm.batch_first
+            xb = (both if bf else both.transpose(0, 1)).contiguous()
+            by_real, by_imag = lstm_pair_forward(self, [self.real_lstm, self.imag_lstm], xb, self.proj_engine)
+            if not bf:
+                by_real, by_imag = by_real.transpose(0, 1), by_imag.transpose(0, 1)
         else:
             # cuDNN RNNs default to TF32 math on CUDA; the parity target is the fp32 reference
             with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
@@ -84,6 +137,7 @@ class ComplexLSTM(nn.Module):
         return merge_real_imag(x, r2r - i2i, r2i + i2r, dim=-1)
 
     rec_kernel = True       # class switch: False forces the stock cuDNN path
+    proj_engine = 'umma'    # input projections: 'umma' (bf16x3 tensor-core GEMM) or 'torch' (fp32 F.linear)
 
     def flatten_parameters(self):
         self.real_lstm.flatten_parameters()

@@ -327,24 +327,43 @@ def test_cl2_roundtrip_and_two_source_block():
     assert rel_l2(chain.cl2_to_nchw(act_y).cpu(), y_ref.cpu()) < 5e-5
 
 
+@pytest.mark.parametrize('proj', ['torch', 'umma'])
 @pytest.mark.parametrize('N,T,cin,hid,layers,batch_first', [(6, 37, 64, 256, 1, True), (3, 20, 128, 256, 2, True),
                                                             (5, 11, 32, 128, 1, False), (300, 9, 64, 256, 1, True)])
-def test_complex_lstm_recurrent_kernel_vs_torch(N, T, cin, hid, layers, batch_first):
-    """csrc/lstm_rec.cu against torch's own fp32 LSTM on the CPU (the reference's arithmetic) and cuDNN."""
+def test_complex_lstm_recurrent_kernel_vs_torch(N, T, cin, hid, layers, batch_first, proj):
+    """csrc/lstm_rec.cu (+ the input projections on the GEMM engine for proj='umma') against torch's own
+    fp32 LSTM on the CPU (the reference's arithmetic) and against cuDNN."""
     m = se.ComplexLSTM(cin, hid, num_layers=layers, batch_first=batch_first)
     sd = {k: rand(v.shape, 4000 + j, 0.3) for j, (k, v) in enumerate(sorted(m.state_dict().items()))}
     m.load_state_dict(sd)
     shape = (N, T, cin) if batch_first else (T, N, cin)
     x = rand(shape, 4100)
+    tol = TOL_EXACT if proj == 'torch' else 3e-5
     with torch.no_grad():
         ref = m(x)                                   # CPU: stock nn.LSTM
         m.to(DEV)
+        m.proj_engine = proj
         n0 = _abi.lib().se_launch_count()
         y = m(x.to(DEV))
-        assert _abi.lib().se_launch_count() - n0 == 2 * layers     # the kernel really ran
+        assert _abi.lib().se_launch_count() - n0 >= 2 * layers     # the kernels really ran
         m.rec_kernel = False
         y_cudnn = m(x.to(DEV))
     assert y.shape == ref.shape
-    assert rel_l2(y.cpu(), ref) < TOL_EXACT
+    assert rel_l2(y.cpu(), ref) < tol
     # cuDNN's own LSTM sits ~1.4e-5 from the CPU result on the 2-layer case (fast-math gates)
     assert rel_l2(y.cpu(), y_cudnn.cpu()) < 5e-5
+
+
+@pytest.mark.parametrize('M,cin,cout', [(7, 256, 1024), (1284, 64, 96), (40, 520, 36)])
+def test_complex_linear_tensor_engine(M, cin, cout):
+    m = se.ComplexLinear(cin, cout)
+    sd = {k: rand(v.shape, 4200 + j, 0.2) for j, (k, v) in enumerate(sorted(m.state_dict().items()))}
+    m.load_state_dict(sd)
+    x = rand((3, M, cin), 4300)
+    with torch.no_grad():
+        ref = m(x)
+        m.to(DEV)
+        y = m(x.to(DEV))
+        m.engine = 'torch'
+        y_t = m(x.to(DEV))
+    assert y.shape == ref.shape and rel_l2(y.cpu(), ref) < 3e-5 and rel_l2(y_t.cpu(), ref) < TOL_EXACT
