@@ -133,6 +133,10 @@ typedef struct se_cconv_args {
    * (conv_stft.py:101-114).                                                                        */
   int64_t y_bs, y_cs, y_hs, y_ws, y_off, y_lim;
   const float* y_scale;
+  /* optional per-source extents (0 = H, W): a source with src_H < H or src_W < W reads as zero beyond its
+   * own bottom / right edge -- the F.pad(x, ...) to the skip's size in front of the decoder layers
+   * (_1903_03107_dcunet.py:89-92, _2206_07293_frcrn.py:97-98), done by TMA out-of-bounds fill.       */
+  int src_H[2], src_W[2];
 } se_cconv_args;
 SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);
 /* fp32 x[b*xs_b + c*xs_c + h*xs_h + w] -> CL2 (same as se_cl2_from_nchw for arbitrary outer strides). */

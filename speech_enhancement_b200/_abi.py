@@ -61,7 +61,8 @@ class ConvArgs(C.Structure):
                 ('wq', C.c_void_p), ('bias', C.c_void_p), ('slope', C.c_float), ('y_nchw', C.c_void_p),
                 ('y_cl2', C.c_void_p), ('y_Cp', C.c_int),
                 ('y_bs', C.c_int64), ('y_cs', C.c_int64), ('y_hs', C.c_int64), ('y_ws', C.c_int64),
-                ('y_off', C.c_int64), ('y_lim', C.c_int64), ('y_scale', C.c_void_p)]
+                ('y_off', C.c_int64), ('y_lim', C.c_int64), ('y_scale', C.c_void_p),
+                ('src_H', C.c_int * 2), ('src_W', C.c_int * 2)]
 
 
 _lib = None

@@ -59,6 +59,13 @@ class _Stack(nn.Module):
         self.layers = nn.ModuleList(layers)
 
 
+def _fusable(model, x, first_block):
+    """the chained engine serves eval / no_grad CUDA calls of models built on this package's conv modules"""
+    name = first_block._layer_name
+    return (model.fused and not model.training and not torch.is_grad_enabled() and x.is_cuda
+            and type(getattr(first_block, name)).__module__.startswith('speech_enhancement_b200'))
+
+
 def _spec_planes(spec, n_bins):
     return spec[:, :n_bins, :], spec[:, n_bins:, :]
 
@@ -245,7 +252,50 @@ class DCUNet(nn.Module):
         dec.append(_Block(ops, True, cin * 2, 2, k, None, stride=s, padding=p))
         self.decoder = _Stack(dec)
 
+    fused = True
+    _fb = None
+
+    def _fused_blocks(self):
+        if self._fb is None:
+            from .chain import FusedBlock
+            first = FusedBlock(self.first_conv.conv, self.first_conv.norm, self.first_conv.act)
+            enc = [FusedBlock(l.conv, l.norm, l.act) for l in self.encoder.layers]
+            dec = []
+            for l in self.decoder.layers:
+                cin2 = 2 * l.conv_transposed.real_conv.weight.shape[0]
+                dec.append(FusedBlock(l.conv_transposed, l.norm, l.act, src_channels=[cin2 // 2, cin2 // 2],
+                                      concat='plain'))
+            self._fb = (first, enc, dec)
+        return self._fb
+
+    def _forward_fused(self, x):
+        """same network with every layer chained in the engine's CL2 format: BN + LeakyReLU folded, the
+        F.pad to the skip's size (dcunet.py:89-92) done by out-of-bounds fill, torch.cat as a second source."""
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)                                               # [B, 2F, T]
+        B, C2, T = spec.shape
+        first, enc, dec = self._fused_blocks()
+        act, _ = first.first_layer(spec, C2 * T, n_bins * T, T, B, n_bins, T)
+        skips = []
+        for blk in enc:
+            act, _ = blk([act])
+            skips.append(act)
+        y = None
+        for i, blk in enumerate(dec):
+            skip = skips.pop()
+            if act.H > skip.H or act.W > skip.W:
+                raise RuntimeError('DCUNet: decoder activation larger than its skip connection')
+            last = i == len(dec) - 1
+            act, y = blk([act, skip], out_cl2=not last, out_nchw=last)
+        y = y[:, :, :n_bins, :T]                                          # dcunet.py:141-146
+        real, imag = _spec_planes(spec, n_bins)
+        est_spec = self._ops.mask_dcunet('bounded_tanh', real, imag, y[:, 0], y[:, 1])
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp_(wav, -1, 1)
+
     def forward(self, x):
+        if not self.normalize and _fusable(self, x, self.first_conv):
+            return self._forward_fused(x)
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)
         real, imag = _spec_planes(spec, n_bins)
@@ -356,7 +406,56 @@ class FRCRN(nn.Module):
         self.lstm = ComplexLSTM(256, lstm_channels, num_layers=2, bidirectional=False, batch_first=True)
         self.final_conv = nn.Conv2d(128, 2, kernel_size=(1, 2), bias=False)
 
+    fused = True
+    _fb = None
+
+    def _fused_blocks(self):
+        if self._fb is None:
+            from .chain import FusedBlock
+            enc = [FusedBlock(l.conv, l.norm, l.act) for l in self.encoder.layers]
+            dec = []
+            for l in self.decoder.layers:
+                cin2 = 2 * l.conv_transposed.real_conv.weight.shape[0]
+                dec.append(FusedBlock(l.conv_transposed, l.norm, l.act, src_channels=[cin2 // 2, cin2 // 2],
+                                      concat='complex'))
+            self._fb = (enc, dec)
+        return self._fb
+
+    def _forward_fused(self, x):
+        """encoder / decoder convolutions chained in CL2 (BN + LeakyReLU folded, causal pad as a coordinate
+        shift, complex_concat as a second source, the bottom-row F.pad by out-of-bounds fill); the CCBAM
+        attention on the skips, the LSTM and the real final_conv keep their own paths."""
+        from .chain import cl2_from_nchw
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)
+        B, C2, T = spec.shape
+        noisy_real, noisy_imag = _spec_planes(spec, n_bins)
+        enc, dec = self._fused_blocks()
+        act, nchw = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1,
+                                       out_nchw=True)
+        skips = [nchw]
+        for i in range(1, len(enc)):
+            act, nchw = enc[i]([act], pad_left=1, out_cl2=True, out_nchw=True)
+            skips.append(nchw)
+        b, c, f, t = nchw.shape
+        h = self.lstm(nchw.reshape(b, c * f, t).permute(0, 2, 1))
+        act = cl2_from_nchw(h.permute(0, 2, 1).reshape(b, c, f, t))
+        y = None
+        n = len(dec)
+        for i, (att, blk) in enumerate(zip(self.decoder.skip_connection_attention_layers, dec)):
+            skip = cl2_from_nchw(att(skips.pop()))
+            if act.W > skip.W:
+                act = act.trimmed(W=skip.W)
+            act, y = blk([act, skip], out_cl2=i < n - 1, out_nchw=i == n - 1)
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            y = self.final_conv(y)                                        # [B, 2, F-2, T]
+        est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, y[:, 0], y[:, 1])
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp_(wav, -1, 1)
+
     def forward(self, x):
+        if _fusable(self, x, self.encoder.layers[0]):
+            return self._forward_fused(x)
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)
         noisy_real, noisy_imag = _spec_planes(spec, n_bins)

@@ -199,9 +199,10 @@ class FusedBlock:
         ops = self._operands()
         if len(srcs) != len(self.src_channels) or any(s.C != c for s, c in zip(srcs, self.src_channels)):
             raise RuntimeError(f'FusedBlock: expected sources with channels {self.src_channels}')
-        H, W, B = srcs[0].H, srcs[0].W, srcs[0].B
-        if any(s.H != H or s.W != W or s.B != B for s in srcs):
-            raise RuntimeError('FusedBlock: sources disagree on their logical extent')
+        # sources may differ in extent: the smaller one is zero-extended at its bottom / right edge
+        H, W, B = max(s.H for s in srcs), max(s.W for s in srcs), srcs[0].B
+        if any(s.B != B for s in srcs):
+            raise RuntimeError('FusedBlock: sources disagree on the batch size')
         Ho, Wo = self.out_size(H, W, pad_top, pad_left)
         dev = srcs[0].data.device
         y_act = cl2_empty(B, self.cout2, Ho, Wo, dev) if out_cl2 else None
@@ -211,6 +212,7 @@ class FusedBlock:
         for i, s in enumerate(srcs):
             a.src[i] = s.data.data_ptr()
             a.src_Cp[i], a.src_Hpitch[i], a.src_Wpitch[i] = s.Cp, s.data.shape[2], s.data.shape[3]
+            a.src_H[i], a.src_W[i] = s.H, s.W
         a.H, a.W, a.pad_top, a.pad_left = H, W, pad_top, pad_left
         a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw, a.Ho, a.Wo = (self.cout2, self.kh, self.kw, self.sh,
                                                                     self.sw, self.ph, self.pw, Ho, Wo)

@@ -778,7 +778,10 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   for (int i = 0; i < 2; ++i) {
     const int j = i < a->nsrc ? i : 0;
     const uint64_t Cp = (uint64_t)a->src_Cp[j];
-    uint64_t dims[4] = {Cp, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)(a->B * 2)};
+    // a source smaller than the logical extent reads as zero beyond its own edge (TMA out-of-bounds fill):
+    // this is the F.pad-to-the-skip's-size of the DCUNet / FRCRN decoders
+    const int sH = a->src_H[j] > 0 ? a->src_H[j] : a->H, sW = a->src_W[j] > 0 ? a->src_W[j] : a->W;
+    uint64_t dims[4] = {Cp, (uint64_t)sW, (uint64_t)sH, (uint64_t)(a->B * 2)};
     uint64_t str[3] = {Cp * 2, (uint64_t)a->src_Wpitch[j] * Cp * 2,
                        (uint64_t)a->src_Hpitch[j] * a->src_Wpitch[j] * Cp * 2};
     uint32_t box[4] = {64, (uint32_t)(tc.TW * p.col_mul), (uint32_t)(rows * p.row_mul), 1};
@@ -893,7 +896,11 @@ extern "C" int se_cconv_gemm(const se_cconv_args* a, void* stream) {
   SE_REQUIRE(a->y_cl2 == nullptr || (a->y_Cp >= a->Cout2 && a->y_Cp % 64 == 0),
              "se_cconv_gemm: y_Cp must be a multiple of 64 >= Cout2");
   for (int i = 0; i < a->nsrc; ++i)
-    SE_REQUIRE(a->src_Hpitch[i] >= a->H && a->src_Wpitch[i] >= a->W, "se_cconv_gemm: source pitch < extent");
+  {
+    const int sH = a->src_H[i] > 0 ? a->src_H[i] : a->H, sW = a->src_W[i] > 0 ? a->src_W[i] : a->W;
+    SE_REQUIRE(sH <= a->H && sW <= a->W, "se_cconv_gemm: a source is larger than the logical extent");
+    SE_REQUIRE(a->src_Hpitch[i] >= sH && a->src_Wpitch[i] >= sW, "se_cconv_gemm: source pitch < extent");
+  }
   if (a->B == 0) return SE_OK;
   return se::cconv_gemm_launch(a, (cudaStream_t)stream);
 }

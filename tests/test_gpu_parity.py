@@ -306,6 +306,35 @@ def test_dccrn_fused_chain_matches_modular_path_and_oracle():
     assert rel_l2(wav_m.cpu(), wav_ref) < 3e-4
 
 
+@pytest.mark.parametrize('cls,args,L', [(callers.DCUNet, ('dcunet20', 512, 128, 512), 20000),
+                                        (callers.DCUNet, ('dcunet10', 512, 128, 512), 16384),
+                                        (callers.DCUNet, ('dcunet16', 400, 100, 512), 16384),
+                                        (callers.FRCRN, (320, 160, 640), 16000)])
+def test_dcunet_frcrn_fused_chain_matches_modular_path_and_oracle(cls, args, L):
+    """the chained engine for the other two complex families: plain torch.cat skips with the F.pad to the
+    skip's size (DCUNet) and CCBAM-attended complex_concat skips (FRCRN)."""
+    ref = cls(*args, ops=OPS).eval()
+    sd = seeded_state_dict(ref, seed=6)
+    ref.load_state_dict(sd)
+    ours = cls(*args).eval()
+    ours.load_state_dict(sd)
+    ours.to(DEV)
+    x = synth_noisy_speech(2, L, seed=10)
+    with torch.no_grad():
+        _, wav_ref = ref(x)
+        calls, chained = [], ours._forward_fused
+        ours._forward_fused = lambda inp: (calls.append(1), chained(inp))[1]
+        spec_f, wav_f = ours(x.to(DEV))
+        ours.fused = False
+        spec_m, wav_m = ours(x.to(DEV))
+    assert len(calls) == 1                      # the first call took the chained path, the second did not
+    assert wav_f.shape == wav_m.shape == wav_ref.shape
+    assert rel_l2(wav_f.cpu(), wav_m.cpu()) < 1e-4
+    assert rel_l2(spec_f.cpu(), spec_m.cpu()) < 1e-4
+    assert rel_l2(wav_f.cpu(), wav_ref) < 3e-4
+    assert rel_l2(wav_m.cpu(), wav_ref) < 3e-4
+
+
 def test_cl2_roundtrip_and_two_source_block():
     from speech_enhancement_b200 import chain
     x = rand((2, 40, 9, 37), 3).to(DEV)
