@@ -32,9 +32,18 @@ sys.path.insert(0, ROOT)
 
 SR, CLIP_S = 16000, 4
 L = SR * CLIP_S
-MODEL_ARGS = ('dccrn-CL', 400, 100, 512)
-CONV_GFLOP_PER_UTT = 65.95          # SURVEY.md 8a, sum 2*M*K*N over the 12 complex conv layers
-METRIC, UNIT = 'dccrn_cl_audio_seconds_enhanced_per_second', 'audio-s/s'
+UNIT = 'audio-s/s'
+# BASELINE.json's metric is quoted on DCCRN (default); the two other complex families of configs[1] / [2]
+# run through the same bench with --model.  conv GFLOP/utt: SURVEY.md 8a/8d (sum of 2*M*K*N per layer).
+MODELS = {
+    'dccrn': dict(cls='DCCRN', args=('dccrn-CL', 400, 100, 512), stft=(400, 100, 512), conv_gflop=65.95,
+                  name='DCCRN-CL', metric='dccrn_cl_audio_seconds_enhanced_per_second', act_mb=268),
+    'dcunet20': dict(cls='DCUNet', args=('dcunet20', 512, 128, 512), stft=(512, 128, 512), conv_gflop=152.99,
+                     name='DCUNet-20', metric='dcunet20_audio_seconds_enhanced_per_second', act_mb=600),
+    'frcrn': dict(cls='FRCRN', args=(320, 160, 640), stft=(320, 160, 640), conv_gflop=97.61,
+                  name='FRCRN', metric='frcrn_audio_seconds_enhanced_per_second', act_mb=500),
+}
+MODEL = MODELS['dccrn']
 
 
 def peaks():
@@ -84,7 +93,7 @@ class ClockSampler:
 def build_models(device, seed=0):
     from speech_enhancement_b200 import callers
     from speech_enhancement_b200.synth import seeded_state_dict
-    model = callers.DCCRN(*MODEL_ARGS)
+    model = getattr(callers, MODEL['cls'])(*MODEL['args'])
     model.load_state_dict(seeded_state_dict(model, seed=seed))
     return model.eval().to(device)
 
@@ -93,7 +102,7 @@ def build_oracle(seed=0):
     from speech_enhancement_b200 import callers
     from speech_enhancement_b200.synth import seeded_state_dict
     from oracle.modules_ref import OPS
-    model = callers.DCCRN(*MODEL_ARGS, ops=OPS)
+    model = getattr(callers, MODEL['cls'])(*MODEL['args'], ops=OPS)
     model.load_state_dict(seeded_state_dict(model, seed=seed))
     return model.eval()
 
@@ -120,11 +129,12 @@ def time_cpu_oracle(batch, iters, warmup=1):
 
 
 def config_dict(batch, n_gpus):
-    return {'workload': f'DCCRN-CL forward (win 400 / hop 100 / fft 512), {batch} x 4 s 16 kHz utterances per GPU, '
-                        'fp32 I/O, eval/no_grad, seeded random-init weights',
+    win, hop, fft = MODEL['stft']
+    return {'workload': f'{MODEL["name"]} forward (win {win} / hop {hop} / fft {fft}), {batch} x 4 s 16 kHz utterances '
+                        'per GPU, fp32 I/O, eval/no_grad, seeded random-init weights',
             'per_gpu_batch': batch, 'global_batch': batch * n_gpus, 'clip_seconds': CLIP_S, 'sample_rate': SR,
             'parallelism': f'utterance-sharded x{n_gpus}, no data-path collective',
-            'l2_policy': 'per-step activation working set (>= 268 MB/utt) exceeds the 126 MB L2; '
+            'l2_policy': f'per-step activation working set (>= {MODEL["act_mb"]} MB/utt) exceeds the 126 MB L2; '
                          'inputs rotate over 3 buffers'}
 
 
@@ -135,7 +145,7 @@ def run_reference(args):
     batch = min(args.batch, 2)
     value, cores, _ = time_cpu_oracle(batch, iters=max(args.steps, 1), warmup=max(args.warmup, 1))
     sec = batch * CLIP_S / value
-    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+    line = {'impl': 'reference', 'metric': MODEL['metric'], 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': config_dict(args.batch, args.gpus),
@@ -178,7 +188,7 @@ class StageTimer:
 
 def run_ours(args):
     import torch.distributed as dist
-    from speech_enhancement_b200 import _abi
+    from speech_enhancement_b200 import _abi, sharding
     from speech_enhancement_b200.synth import synth_noisy_speech
 
     rank = int(os.environ.get('RANK', '0'))
@@ -218,10 +228,7 @@ def run_ours(args):
             fn(i)
         e1.record()
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return ms.item()
+        return sharding.reduce_max(e0.elapsed_time(e1), device=dev)      # the slowest rank defines the step
 
     for i in range(max(args.warmup, 3)):
         step(i)
@@ -266,33 +273,35 @@ def run_ours(args):
     st.close()
     for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm', 'linear'):
         tot.setdefault(k, 0.0)
-    T = (L + 512 - 400) // 100 + 1
-    Lp = out_len or (T - 1) * 100 + 400 - 512
-    alg = {'stft': 4 * (L + 514 * T), 'istft': 4 * (514 * T + Lp), 'mask': 4 * 6 * 257 * T}
+    win, hop, fft = MODEL['stft']
+    T = (L + fft - win) // hop + 1
+    Lp = out_len or (T - 1) * hop + win - fft
+    alg = {'stft': 4 * (L + (fft + 2) * T), 'istft': 4 * ((fft + 2) * T + Lp), 'mask': 4 * 6 * (fft // 2 + 1) * T}
     stages = {}
     for k in ('stft', 'istft', 'mask'):
         t = tot[k] / nprof / 1e3
         gbs = alg[k] * B / t / 1e9
         stages[k] = {'ms': t * 1e3, 'GB/s': gbs, 'frac_hbm': gbs / pk['hbm_gbs']}
     t_conv = tot['cconv'] / nprof / 1e3
-    tflops = CONV_GFLOP_PER_UTT * B / t_conv / 1e3
+    tflops = MODEL['conv_gflop'] * B / t_conv / 1e3
     stages['cconv'] = {'ms': t_conv * 1e3, 'TFLOP/s': tflops, 'launches': len(st.events.get('cconv', [])) // nprof}
     stages['cl2_convert_ms'] = tot['cl2'] / nprof
     stages['lstm_recurrence_ms'] = tot['lstm'] / nprof
     stages['lstm_linear_projections_ms'] = tot['linear'] / nprof
     stages['step_ms'] = ms / args.steps
     stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / args.steps)
-    roofline = {'bound': 'tensor', 'kernel': 'complex conv stack (12 se_cconv*_fwd launches per step)',
+    roofline = {'bound': 'tensor', 'kernel': f'complex conv stack ({len(st.events.get("cconv", [])) // nprof} conv launches per step)',
                 'achieved': tflops, 'peak': pk['bf16_tflops_sustained'], 'unit': 'TFLOP/s',
                 'frac': tflops / pk['bf16_tflops_sustained'],
                 # dram__bytes_read + write summed over the 11 conv GEMM launches of one step, from the ncu --set full
                 # capture profiles/r1c_gemm_full_summary.txt (B=64: 25.46 GB), scaled per utterance
-                'traffic': 25.458e9 / 64 * B, 'traffic_unit': 'B per step (all conv GEMM launches)',
+                'traffic': 25.458e9 / 64 * B if args.model == 'dccrn' else None,
+                'traffic_unit': 'B per step (all conv GEMM launches)',
                 'peak_source': pk['source'] + ' bf16 dense (sustained)',
-                'note': 'algorithmic FLOPs (65.95 GFLOP/utt); the tensor engine issues 3 bf16 passes per product'}
+                'note': f'algorithmic FLOPs ({MODEL["conv_gflop"]} GFLOP/utt); the tensor engine issues 3 bf16 passes per product'}
 
     cpu_val, cores, cpu_sec = time_cpu_oracle(2, iters=5, warmup=1)
-    line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+    line = {'metric': MODEL['metric'], 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32 (bf16x3 split operands, fp32 accumulate)',
             'data': 'synthetic', 'config': config_dict(B, world),
@@ -315,7 +324,10 @@ def main():
     ap.add_argument('--batch', type=int, default=int(os.environ.get('SE_BENCH_BATCH', '64')),
                     help='4 s utterances per GPU per step')
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--model', default=os.environ.get('SE_BENCH_MODEL', 'dccrn'), choices=sorted(MODELS))
     args = ap.parse_args()
+    global MODEL
+    MODEL = MODELS[args.model]
     if args.impl == 'reference':
         run_reference(args)
     else:
