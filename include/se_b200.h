@@ -165,6 +165,15 @@ SE_API int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, int64_
                               float slope, int Cout2, int kh, int kw, int sh, int sw, int ph, int pw,
                               float* y_nchw, void* y_cl2, int y_Cp, int Ho, int Wo, void* stream);
 
+/* Gather step of the scatter-form transposed convolution for layers with 2 or 4 output channels (last
+ * decoder layer of DCCRN / DCUNet, _2008_00264_dccrn.py:104-111, _1903_03107_dcunet.py:79-81):
+ * P [B][H][W][Np] holds, per INPUT pixel, the products with every tap (column tap*Cout2 + co; produced by
+ * se_cconv_gemm as a 1x1 convolution with taps*Cout2 output columns);
+ * y[b,co,ho,wo] = act(bias[co] + sum of the P entries whose tap lands on (ho, wo)).                   */
+SE_API int se_cconvT_col2im(const float* P, int64_t B, int H, int W, int Np, int Cout2, int kh, int kw, int sh,
+                            int sw, int ph, int pw, int Ho, int Wo, const float* bias, float slope, float* y,
+                            void* stream);
+
 /* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
  * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),
  * so slices of the STFT output and of the decoder output are consumed in place.  For

@@ -136,6 +136,9 @@ class FusedBlock:
         if sum(self.src_channels) != self.cin2:
             raise RuntimeError(f'FusedBlock: sources {self.src_channels} do not add up to {self.cin2} channels')
         self.concat = concat
+        # transposed layers with 2 or 4 output channels run in scatter form (1x1 GEMM over the taps + gather):
+        # one pass over the input instead of one >= 84-cycle MMA per tap for a handful of useful columns
+        self.scatter_form = self.transposed and self.cout2 in (2, 4) and self.kh * self.kw * self.cout2 <= 128
         self._key = None
         self._ops = None
 
@@ -183,7 +186,15 @@ class FusedBlock:
             with torch.cuda.device(dev):
                 _abi.check(lib.se_cconv_prep_weight(_abi.ptr(packed), 2 * co, 2 * ci, taps, _abi.ptr(cmap_t), cpt,
                                                     _abi.ptr(wq), _abi.stream_ptr()))
-        self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt}
+            wq_sc = None
+            if self.scatter_form:
+                # taps folded into the output columns of a 1x1 convolution: row tap*2co + o <- packed[o, :, tap]
+                p3 = packed.view(2 * co, 2 * ci, taps).permute(2, 0, 1).reshape(taps * 2 * co, 2 * ci).contiguous()
+                wq_sc = torch.empty((lib.se_cconv_wq_elems(taps * 2 * co, cpt, 1),), device=dev, dtype=torch.bfloat16)
+                with torch.cuda.device(dev):
+                    _abi.check(lib.se_cconv_prep_weight(_abi.ptr(p3), taps * 2 * co, 2 * ci, 1, _abi.ptr(cmap_t), cpt,
+                                                        _abi.ptr(wq_sc), _abi.stream_ptr()))
+        self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt, 'wq_sc': wq_sc}
         self._key = key
         return self._ops
 
@@ -220,6 +231,21 @@ class FusedBlock:
         a.y_nchw = y.data_ptr() if y is not None else None
         a.y_cl2 = y_act.data.data_ptr() if y_act is not None else None
         a.y_Cp = y_act.Cp if y_act is not None else 0
+        if self.scatter_form and out_nchw and not out_cl2:
+            ncol = self.kh * self.kw * self.cout2
+            Np = (ncol + 3) // 4 * 4
+            P = torch.empty((B, H, W, Np), device=dev, dtype=torch.float32)
+            a.transposed, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw, a.Ho, a.Wo = 0, ncol, 1, 1, 1, 1, 0, 0, H, W
+            a.wq, a.bias, a.slope = ops['wq_sc'].data_ptr(), None, 1.0
+            a.y_nchw = P.data_ptr()
+            a.y_cs, a.y_ws, a.y_hs, a.y_bs = 1, Np, W * Np, H * W * Np
+            with torch.cuda.device(dev), _abi.stage('cconv'):
+                lib = _abi.lib()
+                _abi.check(lib.se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+                _abi.check(lib.se_cconvT_col2im(_abi.ptr(P), B, H, W, Np, self.cout2, self.kh, self.kw, self.sh, self.sw,
+                                                self.ph, self.pw, Ho, Wo, _abi.ptr(ops['bias']), ops['slope'],
+                                                _abi.ptr(y), _abi.stream_ptr()))
+            return None, y
         with torch.cuda.device(dev), _abi.stage('cconv'):
             _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
         return y_act, y

@@ -217,3 +217,80 @@ int cconv_fwd_small_cout(bool transposed, const float* x, const float* packed, c
 }
 
 }  // namespace se
+
+
+// ------------------------------------------------------------------------------------------------
+// Scatter form of a transposed convolution with very few output channels (the last decoder layer of
+// DCCRN / DCUNet: Cout2 = 2; /root/reference/models/_2008_00264_dccrn.py:104-111,
+// _1903_03107_dcunet.py:79-81).  On the tensor cores such a layer costs one >= 84-cycle MMA per tap and
+// k-step for a handful of useful columns; instead the taps are folded into the GEMM's N dimension
+// (a 1x1 convolution with taps*Cout2 output columns, one pass over the input, no shifted re-reads):
+//   P[b, hi, wi, tap*Cout2 + co] = sum_c x[b, c, hi, wi] * w[c, co, tap]
+// and this kernel gathers the partial products that land on every output pixel:
+//   y[b, co, ho, wo] = act(bias[co] + sum_{dh,dw : sh | ho+ph-dh, sw | wo+pw-dw} P[b, (ho+ph-dh)/sh, (wo+pw-dw)/sw, ...])
+namespace se {
+
+struct Col2imParams {
+  const float* P; float* y; const float* bias;
+  int64_t B; int H, W, Np, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo;
+  float slope;
+};
+
+template <int CO>
+__global__ void __launch_bounds__(256)
+col2im_small_kernel(const Col2imParams p) {
+  const int64_t total = p.B * p.Ho * (int64_t)p.Wo;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int wo = (int)(i % p.Wo);
+    const int64_t r = i / p.Wo;
+    const int ho = (int)(r % p.Ho);
+    const int64_t b = r / p.Ho;
+    float acc[CO];
+#pragma unroll
+    for (int c = 0; c < CO; ++c) acc[c] = p.bias != nullptr ? __ldg(p.bias + c) : 0.f;
+    for (int dh = 0; dh < p.kh; ++dh) {
+      const int nh = ho + p.ph - dh;
+      if (nh < 0 || nh % p.sh != 0) continue;
+      const int hi = nh / p.sh;
+      if (hi >= p.H) continue;
+      for (int dw = 0; dw < p.kw; ++dw) {
+        const int nw = wo + p.pw - dw;
+        if (nw < 0 || nw % p.sw != 0) continue;
+        const int wi = nw / p.sw;
+        if (wi >= p.W) continue;
+        const float* src = p.P + ((b * p.H + hi) * p.W + wi) * p.Np + (dh * p.kw + dw) * CO;
+        if (CO == 2) {
+          const float2 v = __ldg(reinterpret_cast<const float2*>(src));
+          acc[0] += v.x; acc[1] += v.y;
+        } else {
+#pragma unroll
+          for (int c = 0; c < CO; ++c) acc[c] += __ldg(src + c);
+        }
+      }
+    }
+    const int64_t plane = (int64_t)p.Ho * p.Wo;
+#pragma unroll
+    for (int c = 0; c < CO; ++c) {
+      const float v = acc[c];
+      p.y[(b * CO + c) * plane + (int64_t)ho * p.Wo + wo] = v > 0.f ? v : v * p.slope;
+    }
+  }
+}
+
+}  // namespace se
+
+extern "C" int se_cconvT_col2im(const float* P, int64_t B, int H, int W, int Np, int Cout2, int kh, int kw, int sh,
+                                int sw, int ph, int pw, int Ho, int Wo, const float* bias, float slope, float* y,
+                                void* stream) {
+  SE_REQUIRE(P && y, "se_cconvT_col2im: null pointer");
+  SE_REQUIRE(B >= 0 && H > 0 && W > 0 && kh > 0 && kw > 0 && sh > 0 && sw > 0 && Ho > 0 && Wo > 0 &&
+             Np >= kh * kw * Cout2 && Np % 2 == 0, "se_cconvT_col2im: bad dims");
+  if (Cout2 != 2 && Cout2 != 4) return se::fail(SE_ERR_UNSUPPORTED, "se_cconvT_col2im: Cout2 must be 2 or 4");
+  if (B == 0) return SE_OK;
+  se::Col2imParams p{P, y, bias, B, H, W, Np, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo, slope};
+  const int64_t total = B * Ho * (int64_t)Wo;
+  const unsigned blocks = (unsigned)std::min<int64_t>((total + 255) / 256, (int64_t)se::num_sms() * 32);
+  if (Cout2 == 2) se::col2im_small_kernel<2><<<blocks, 256, 0, (cudaStream_t)stream>>>(p);
+  else se::col2im_small_kernel<4><<<blocks, 256, 0, (cudaStream_t)stream>>>(p);
+  return se::check_launch("se_cconvT_col2im");
+}
