@@ -197,6 +197,11 @@ SE_API int se_lstm_rec_supported(int H);
 SE_API int se_lstm_rec_fwd(const float* pre_gates, int64_t pre_ld, const float* w_hh, int64_t N, int64_t T, int H,
                            float* h_out, void* stream);
 
+/* two LSTMs over the same input in one launch (the real_lstm / imag_lstm of a ComplexLSTM layer,
+ * complex_nn.py:131-142): LSTM i reads pre-gate columns [i*4H, (i+1)*4H) and writes h_out<i> [N][T][H]. */
+SE_API int se_lstm_rec_pair_fwd(const float* pre_gates, int64_t pre_ld, const float* w_hh0, const float* w_hh1,
+                                int64_t N, int64_t T, int H, float* h_out0, float* h_out1, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

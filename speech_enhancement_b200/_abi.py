@@ -44,6 +44,7 @@ _SIGS = {
                            + [_P, _P, _I, _I, _I, _P]),
     'se_lstm_rec_supported': (C.c_int, [_I]),
     'se_lstm_rec_fwd': (C.c_int, [_P, _L, _P, _L, _L, _I, _P, _P]),
+    'se_lstm_rec_pair_fwd': (C.c_int, [_P, _L, _P, _P, _L, _L, _I, _P, _P, _P]),
     'se_cl2_from_rows': (C.c_int, [_P, _L, _I, _L, _P, _I, _P]),
     'se_cconvT_col2im': (C.c_int, [_P, _L] + [_I] * 12 + [_P, C.c_float, _P, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),

@@ -24,9 +24,14 @@ __device__ __forceinline__ float tanhf_(float x) { return tanhf(x); }
 
 template <int H, int KR, int R>
 __global__ void __launch_bounds__(4 * H, 1)
-lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, float* __restrict__ h_out,
-                int64_t N, int64_t T, int64_t pre_ld) {
+lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, const float* __restrict__ w_hh1,
+                float* __restrict__ h_out0, float* __restrict__ h_out1, int64_t N, int64_t T, int64_t pre_ld) {
   constexpr int G = 4 * H, KS = H - KR;
+  // blockIdx.y selects one of two LSTMs that share the pre-gate matrix (columns [0,4H) and [4H,8H)):
+  // the real / imaginary LSTMs of a ComplexLSTM layer run side by side in one launch
+  const float* __restrict__ w_hh = blockIdx.y ? w_hh1 : w_hh0;
+  float* __restrict__ h_out = blockIdx.y ? h_out1 : h_out0;
+  pre += blockIdx.y * G;
   extern __shared__ __align__(16) float smem[];
   float* w_s = smem;                 // [KS][G]
   float* h_s = w_s + KS * G;         // [R][H]
@@ -107,8 +112,8 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, f
 }
 
 template <int H, int KR, int R>
-static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh, float* h_out, int64_t N, int64_t T,
-                       cudaStream_t s) {
+static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh0, const float* w_hh1, float* h_out0,
+                       float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
   constexpr int G = 4 * H;
   const int smem = ((H - KR) * G + R * H + R * G) * (int)sizeof(float);
   static bool attr_set = false;
@@ -117,8 +122,9 @@ static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh, floa
     attr_set = true;
   }
   int64_t ctas = (N + R - 1) / R;
-  if (ctas > num_sms()) ctas = num_sms();
-  lstm_rec_kernel<H, KR, R><<<(unsigned)ctas, G, smem, s>>>(pre, w_hh, h_out, N, T, pre_ld);
+  if (ctas * nl > num_sms()) ctas = num_sms() / nl;
+  lstm_rec_kernel<H, KR, R><<<dim3((unsigned)ctas, (unsigned)nl), G, smem, s>>>(pre, w_hh0, w_hh1, h_out0, h_out1, N, T,
+                                                                                pre_ld);
   return check_launch("lstm_rec_kernel");
 }
 
@@ -126,22 +132,34 @@ static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh, floa
 
 extern "C" int se_lstm_rec_supported(int H) { return (H == 128 || H == 64) ? 1 : 0; }
 
+template <int H, int KR>
+static int dispatch_rows(const float* pre, int64_t pre_ld, const float* w0, const float* w1, float* h0, float* h1, int nl,
+                         int64_t N, int64_t T, cudaStream_t s) {
+  const int64_t sms = se::num_sms(), jobs = N * nl;
+  if (jobs <= sms) return se::launch_lstm<H, KR, 1>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+  if (jobs <= 2 * sms) return se::launch_lstm<H, KR, 2>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+  return se::launch_lstm<H, KR, 4>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+}
+
+static int lstm_rec_any(const float* pre, int64_t pre_ld, const float* w0, const float* w1, float* h0, float* h1, int nl,
+                        int64_t N, int64_t T, int H, cudaStream_t s) {
+  if (H == 128) return dispatch_rows<128, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+  if (H == 64) return dispatch_rows<64, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+  return se::fail(SE_ERR_UNSUPPORTED, "se_lstm_rec_fwd: hidden size %d not supported (64 or 128)", H);
+}
+
 extern "C" int se_lstm_rec_fwd(const float* pre_gates, int64_t pre_ld, const float* w_hh, int64_t N, int64_t T, int H,
                                float* h_out, void* stream) {
   SE_REQUIRE(pre_gates && w_hh && h_out, "se_lstm_rec_fwd: null pointer");
   SE_REQUIRE(N >= 0 && T >= 0 && H > 0 && pre_ld >= 4 * (int64_t)H, "se_lstm_rec_fwd: bad dims");
   if (N == 0 || T == 0) return SE_OK;
-  cudaStream_t s = (cudaStream_t)stream;
-  const int sms = se::num_sms();
-  if (H == 128) {
-    if (N <= sms) return se::launch_lstm<128, 64, 1>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
-    if (N <= 2 * sms) return se::launch_lstm<128, 64, 2>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
-    return se::launch_lstm<128, 64, 4>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
-  }
-  if (H == 64) {
-    if (N <= sms) return se::launch_lstm<64, 64, 1>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
-    if (N <= 2 * sms) return se::launch_lstm<64, 64, 2>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
-    return se::launch_lstm<64, 64, 4>(pre_gates, pre_ld, w_hh, h_out, N, T, s);
-  }
-  return se::fail(SE_ERR_UNSUPPORTED, "se_lstm_rec_fwd: hidden size %d not supported (64 or 128)", H);
+  return lstm_rec_any(pre_gates, pre_ld, w_hh, w_hh, h_out, h_out, 1, N, T, H, (cudaStream_t)stream);
+}
+
+extern "C" int se_lstm_rec_pair_fwd(const float* pre_gates, int64_t pre_ld, const float* w_hh0, const float* w_hh1,
+                                    int64_t N, int64_t T, int H, float* h_out0, float* h_out1, void* stream) {
+  SE_REQUIRE(pre_gates && w_hh0 && w_hh1 && h_out0 && h_out1, "se_lstm_rec_pair_fwd: null pointer");
+  SE_REQUIRE(N >= 0 && T >= 0 && H > 0 && pre_ld >= 8 * (int64_t)H, "se_lstm_rec_pair_fwd: bad dims");
+  if (N == 0 || T == 0) return SE_OK;
+  return lstm_rec_any(pre_gates, pre_ld, w_hh0, w_hh1, h_out0, h_out1, 2, N, T, H, (cudaStream_t)stream);
 }

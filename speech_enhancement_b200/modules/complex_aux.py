@@ -58,8 +58,17 @@ def lstm_pair_forward(owner, lstms, x, engine):
         else:
             pre = torch.cat([F.linear(x2, _lstm_layer_params(m, 0)[0],
                                       sum(_lstm_layer_params(m, 0)[2]) if m.bias else None) for m in lstms], 1)
+        first = None
+        if len(lstms) == 2:
+            # both time loops in one launch (grid.y = LSTM)
+            first = [torch.empty((N, T, H), device=x.device, dtype=torch.float32) for _ in lstms]
+            with _abi.stage('lstm'):
+                _abi.check(_abi.lib().se_lstm_rec_pair_fwd(
+                    _abi.ptr(pre), pre.stride(0), _abi.ptr(_lstm_layer_params(lstms[0], 0)[1].contiguous()),
+                    _abi.ptr(_lstm_layer_params(lstms[1], 0)[1].contiguous()), N, T, H, _abi.ptr(first[0]),
+                    _abi.ptr(first[1]), _abi.stream_ptr()))
         for i, m in enumerate(lstms):
-            h = _lstm_rec(pre, i * 4 * H, _lstm_layer_params(m, 0)[1], N, T, H)
+            h = first[i] if first is not None else _lstm_rec(pre, i * 4 * H, _lstm_layer_params(m, 0)[1], N, T, H)
             for layer in range(1, L):
                 w_ih, w_hh, bias = _lstm_layer_params(m, layer)
                 if engine == 'umma':

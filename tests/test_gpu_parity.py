@@ -374,7 +374,7 @@ def test_complex_lstm_recurrent_kernel_vs_torch(N, T, cin, hid, layers, batch_fi
         m.proj_engine = proj
         n0 = _abi.lib().se_launch_count()
         y = m(x.to(DEV))
-        assert _abi.lib().se_launch_count() - n0 >= 2 * layers     # the kernels really ran
+        assert _abi.lib().se_launch_count() - n0 >= layers         # the kernels really ran
         m.rec_kernel = False
         y_cudnn = m(x.to(DEV))
     assert y.shape == ref.shape
