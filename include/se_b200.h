@@ -185,6 +185,16 @@ SE_API int se_mask_fwd(int kind,
                 const float* mi, int64_t mi_bs, int64_t mi_fs,
                 int64_t B, int F, int64_t T, float* out, void* stream);
 
+/* backward of se_mask_fwd (what autograd derives from the reference's pointwise graph): grad_out
+ * [B, 2F, T] -> d_nr, d_ni [B, F, T] and d_mr, d_mi [B, Fm, T] (Fm = F-2 for SE_MASK_FRCRN), contiguous. */
+SE_API int se_mask_bwd(int kind,
+                const float* nr, int64_t nr_bs, int64_t nr_fs,
+                const float* ni, int64_t ni_bs, int64_t ni_fs,
+                const float* mr, int64_t mr_bs, int64_t mr_fs,
+                const float* mi, int64_t mi_bs, int64_t mi_fs,
+                int64_t B, int F, int64_t T, const float* grad_out, float* d_nr, float* d_ni,
+                float* d_mr, float* d_mi, void* stream);
+
 /* polar -> rectangular (conv_stft.py:96-100): mags, phase [B,F,T] -> spec [B,2F,T] */
 SE_API int se_polar_to_rect(const float* mags, const float* phase, int64_t B, int F, int64_t T,
                      float* spec, void* stream);

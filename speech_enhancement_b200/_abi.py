@@ -48,6 +48,7 @@ _SIGS = {
     'se_cl2_from_rows': (C.c_int, [_P, _L, _I, _L, _P, _I, _P]),
     'se_cconvT_col2im': (C.c_int, [_P, _L] + [_I] * 12 + [_P, C.c_float, _P, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
+    'se_mask_bwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P, _P, _P, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),
 }
 

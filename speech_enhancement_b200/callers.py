@@ -480,3 +480,119 @@ class FRCRN(nn.Module):
         est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, x[:, 0], x[:, 1])
         wav = self.istft(est_spec)
         return est_spec, torch.clamp_(wav, -1, 1)
+
+
+# ------------------------------------------------------------------------------------ CARN
+class _GLU(nn.Module):
+    """carn.py:9-27: conv(x) * sigmoid(conv'(x)); attribute names follow the reference per flavour."""
+
+    def __init__(self, transposed, cin, cout, kernel, **kw):
+        super().__init__()
+        mk = nn.ConvTranspose2d if transposed else nn.Conv2d
+        self._names = ('conv_transpose1', 'conv_transpose2') if transposed else ('conv1', 'conv2')
+        setattr(self, self._names[0], mk(cin, cout, kernel, **kw))
+        setattr(self, self._names[1], mk(cin, cout, kernel, **kw))
+
+    def forward(self, x):
+        return getattr(self, self._names[0])(x) * torch.sigmoid(getattr(self, self._names[1])(x))
+
+
+class _RealBlock(nn.Module):
+    """carn.py:30-56: real conv / convT (+ optional gate) -> BatchNorm2d -> PReLU.  Stock PyTorch: the real
+    convolutions of CARN are outside the hot path."""
+
+    def __init__(self, transposed, cin, cout, kernel, gate=False, **kw):
+        super().__init__()
+        name = 'conv_transposed' if transposed else 'conv'
+        if gate:
+            layer = _GLU(transposed, cin, cout, kernel, bias=False, **kw)
+        else:
+            layer = (nn.ConvTranspose2d if transposed else nn.Conv2d)(cin, cout, kernel, bias=False, **kw)
+        setattr(self, name, layer)
+        self._name = name
+        self.norm = nn.BatchNorm2d(cout)
+        self.act = nn.PReLU()
+
+    def forward(self, x):
+        return self.act(self.norm(getattr(self, self._name)(x)))
+
+
+class _CarnAttention(nn.Module):
+    """carn.py:59-78."""
+
+    def __init__(self, c):
+        super().__init__()
+        self.conv1 = nn.Conv2d(c, c * 2, 3, padding=1, bias=False)
+        self.conv2 = nn.Conv2d(c, c * 2, 3, padding=1, bias=False)
+        self.conv3 = nn.Conv2d(c * 2, c, 3, padding=1, bias=False)
+
+    def forward(self, x_u, x_c):
+        gate = torch.sigmoid(self.conv3(torch.sigmoid(self.conv1(x_u) + self.conv2(x_c))))
+        return gate * x_c
+
+
+class _CarnDecoder(nn.Module):
+    def __init__(self, cin=128, gate=False):
+        super().__init__()
+        self.conv_transpose_layers, self.attention_layers = nn.ModuleList(), nn.ModuleList()
+        for cout in (128, 96, 64, 32, 16, 2):
+            self.attention_layers.append(_CarnAttention(cin))
+            self.conv_transpose_layers.append(_RealBlock(True, cin * 2, cout, (1, 3), gate=gate, stride=(2, 1),
+                                                         padding=(0, 1), output_padding=(1, 0)))
+            cin = cout
+
+
+class CARN(nn.Module):
+    """CARN / GCARN (carn.py:122-178): real-valued encoder / decoder with attention skips around a 2-layer
+    LSTM; the hot-path pieces are the STFT, the complex mask with the reference's sign quirk, and the iSTFT.
+    All three carry autograd, so this model trains (BASELINE config 4)."""
+
+    def __init__(self, window_size=320, hop_size=160, fft_size=512, lstm_channels=512, gate=False, ops=None):
+        super().__init__()
+        ops = ops or cuda_ops()
+        self._ops = ops
+        self.fft_size = fft_size
+        self.stft = ops.ConvSTFT(window_size, hop_size, fft_size)
+        self.istft = ops.ConviSTFT(window_size, hop_size, fft_size)
+        enc, cin = [], 2
+        for cout in (16, 32, 64, 96, 128, 128):
+            enc.append(_RealBlock(False, cin, cout, (3, 3), gate=gate, stride=(2, 1), padding=(1, 1)))
+            cin = cout
+        self.encoder = _Stack(enc)
+        self.decoder = _CarnDecoder(128, gate)
+        self.lstm = nn.LSTM(input_size=lstm_channels, hidden_size=lstm_channels, num_layers=2, batch_first=True)
+        self.linear = nn.Linear(fft_size, fft_size + 2)
+
+    def forward(self, x):
+        n_bins = self.fft_size // 2 + 1
+        spec = self.stft(x)
+        noisy_real, noisy_imag = _spec_planes(spec, n_bins)
+        x = torch.stack([noisy_real, noisy_imag], dim=1)[:, :, 1:, :]
+        skips = []
+        # the real convolutions / LSTM are stock cuDNN; fp32 math (no TF32) in the forward.  For the backward
+        # the caller sets torch.backends.cudnn.allow_tf32 (bench / tests turn it off).
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            for layer in self.encoder.layers:
+                x = layer(x)
+                skips.append(x)
+            b, c, f, t = x.shape
+            x, _ = self.lstm(x.reshape(b, c * f, t).permute(0, 2, 1))
+            x = x.permute(0, 2, 1).reshape(b, c, f, t)
+            for att, layer in zip(self.decoder.attention_layers, self.decoder.conv_transpose_layers):
+                skip = skips.pop()
+                if x.shape[2] < skip.shape[2]:
+                    x = F.pad(x, (0, 0, 0, 1))
+                x = layer(torch.cat([att(x, skip), skip], dim=1))
+        b, c, f, t = x.shape
+        x = self.linear(x.reshape(b, c * f, t).permute(0, 2, 1))
+        x = x.permute(0, 2, 1).reshape(b, 2, n_bins, t)
+        est_spec = self._ops.mask_carn(noisy_real, noisy_imag, x[:, 0], x[:, 1])
+        wav = self.istft(est_spec)
+        return est_spec, torch.clamp(wav, -1, 1)
+
+
+class GCARN(CARN):
+    """carn.py:174-178."""
+
+    def __init__(self, window_size=320, hop_size=160, fft_size=512, lstm_channels=512, ops=None):
+        super().__init__(window_size, hop_size, fft_size, lstm_channels, gate=True, ops=ops)

@@ -62,6 +62,98 @@ def _no_grad_only(name, *tensors):
                            'call under torch.no_grad() / with inputs that do not require grad')
 
 
+def _frames_operand(w, hop):
+    """basis [C2, 1, win] regrouped for the framing projection (a 1 x J convolution over hop-sample pixels,
+    `hop` input channels): [C2][hop][J], output rows in chunks of <= 256."""
+    c2, _, win = w.shape
+    J = -(-win // hop)
+    Cp = _round_up(hop, 64)
+    wp = F.pad(w[:, 0, :], (0, J * hop - win)).view(c2, J, hop).permute(0, 2, 1).contiguous()
+    chunks = []
+    for c0 in range(0, c2, 256):
+        n = min(256, c2 - c0)
+        chunks.append((c0, n, _prep_wq(wp[c0:c0 + n].contiguous(), n, hop, J, Cp)))
+    return J, Cp, chunks
+
+
+def _ola_operand(w, hop):
+    """basis [C2, 1, win] regrouped for overlap-add (a 1 x J convolution over frames with C2 input channels
+    and one output channel per hop phase): [hop][C2][J];  y[q*hop + r] = sum_j sum_c W[c, j*hop + r] spec[c, q-j]."""
+    c2, _, win = w.shape
+    J = -(-win // hop)
+    Cp = _round_up(c2, 64)
+    wp = F.pad(w[:, 0, :], (0, J * hop - win)).view(c2, J, hop).flip(1).permute(2, 0, 1).contiguous()
+    return J, Cp, _prep_wq(wp, hop, c2, J, Cp)
+
+
+def _frames_project(x, operand, hop, pad, T, out):
+    """out[b, c, t] = sum_k W[c, k] * reflect_pad(x, pad)[b, t*hop + k]  (conv_stft.py:60-63)"""
+    B, L = x.shape
+    c2 = out.shape[1]
+    J, Cp, chunks = operand
+    Q = T + J - 1
+    frames = torch.empty((1, 2, B, Q, Cp), device=x.device, dtype=torch.bfloat16)
+    _abi.check(_abi.lib().se_stft_frames_cl2(_abi.ptr(x), B, L, hop, pad, Q, Cp, _abi.ptr(frames), _abi.stream_ptr()))
+    for c0, n, wq in chunks:
+        a = _abi.ConvArgs()
+        a.transposed, a.B, a.nsrc = 0, 1, 1
+        a.src[0] = frames.data_ptr()
+        a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, B, Q
+        a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.Ho, a.Wo = B, Q, n, 1, J, 1, 1, B, T
+        a.wq, a.bias, a.slope = wq.data_ptr(), None, 1.0
+        a.y_nchw = out.data_ptr() + 4 * c0 * T
+        a.y_cs, a.y_hs, a.y_ws = T, c2 * T, 1            # out[b=row, c0 + co, t]
+        _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+
+
+def _overlap_add(spec, operand, hop, scale, out, start, out_len):
+    """out[b, n - start] = scale[n] * sum_t sum_c W[c, n - t*hop] * spec[b, c, t]  (conv_stft.py:99-114)"""
+    B, c2, T = spec.shape
+    J, Cp, wq = operand
+    img = torch.empty((1, 2, B, T, Cp), device=spec.device, dtype=torch.bfloat16)
+    _abi.check(_abi.lib().se_cl2_from_strided(_abi.ptr(spec), 0, T, c2 * T, 1, c2, B, T, _abi.ptr(img), Cp,
+                                              _abi.stream_ptr()))
+    a = _abi.ConvArgs()
+    a.transposed, a.B, a.nsrc = 0, 1, 1
+    a.src[0] = img.data_ptr()
+    a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, B, T
+    a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw = B, T, hop, 1, J, 1, 1, 0, J - 1
+    a.Ho, a.Wo = B, T + J - 1
+    a.wq, a.bias, a.slope = wq.data_ptr(), None, 1.0
+    a.y_nchw = out.data_ptr()
+    a.y_cs, a.y_hs, a.y_ws, a.y_off, a.y_lim = 1, out_len, hop, -start, out_len
+    a.y_scale = scale.data_ptr() if scale is not None else None
+    _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+
+
+class _StftFn(torch.autograd.Function):
+    """ConvSTFT as one autograd node.  The op is linear, so the backward is the adjoint: overlap-add of the
+    gradient frames with the SAME basis, folded back through the reflect padding."""
+
+    @staticmethod
+    def forward(ctx, mod, x):
+        ctx.mod, ctx.L = mod, x.shape[1]
+        return mod._project(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return None, ctx.mod._project_adjoint(g.contiguous().float(), ctx.L)
+
+
+class _IstftFn(torch.autograd.Function):
+    """ConviSTFT as one autograd node; backward = framing projection of the normalised, un-cropped gradient
+    with the inverse basis."""
+
+    @staticmethod
+    def forward(ctx, mod, spec, start, out_len):
+        ctx.mod, ctx.T, ctx.start = mod, spec.shape[2], start
+        return mod._synthesize(spec, start, out_len)
+
+    @staticmethod
+    def backward(ctx, g):
+        return None, ctx.mod._synthesize_adjoint(g.contiguous().float(), ctx.T, ctx.start), None, None
+
+
 class ConvSTFT(nn.Module):
     def __init__(self, window_size, hop_size, fft_size=None, win_type='hann', center=True,
                  return_mag_phase=False, fix=True):
@@ -79,45 +171,59 @@ class ConvSTFT(nn.Module):
 
     engine = 'auto'
 
-    def _tc_operands(self, w):
-        """basis regrouped for the conv engine: the framed convolution (conv_stft.py:63) over hop-sample
-        pixels is a 1 x J convolution with `hop` input channels; output rows go in chunks of <= 256."""
-        key = (w.data_ptr(), w._version, w.device)
-        if self._tc_key != key:
-            c2, _, win = w.shape
-            hop = self.hop_size
-            J = -(-win // hop)
-            Cp = _round_up(hop, 64)
-            wp = F.pad(w[:, 0, :], (0, J * hop - win)).view(c2, J, hop).permute(0, 2, 1).contiguous()
-            chunks = []
-            for c0 in range(0, c2, 256):
-                n = min(256, c2 - c0)
-                chunks.append((c0, n, _prep_wq(wp[c0:c0 + n].contiguous(), n, hop, J, Cp)))
-            self._tc, self._tc_key = (J, Cp, chunks), key
-        return self._tc
+    def _cached(self, slot, build):
+        w = self.weight
+        key = (slot, w.data_ptr(), w._version, w.device)
+        c = self.__dict__.setdefault('_tc_cache', {})
+        if c.get(slot, (None,))[0] != key:
+            with torch.no_grad():
+                c[slot] = (key, build(w.detach().contiguous(), self.hop_size))
+        return c[slot][1]
 
-    def _forward_tc(self, x, w, out, T, pad):
+    def _project(self, x):
+        """[B, L] -> [B, C2, T] (+ nothing else): the tensor-core framing projection or the SIMT kernel"""
+        w = self.weight
         B, L = x.shape
-        c2 = w.shape[0]
-        J, Cp, chunks = self._tc_operands(w)
-        Q = T + J - 1
-        frames = torch.empty((1, 2, B, Q, Cp), device=x.device, dtype=torch.bfloat16)
-        _abi.check(_abi.lib().se_stft_frames_cl2(_abi.ptr(x), B, L, self.hop_size, pad, Q, Cp, _abi.ptr(frames),
-                                                 _abi.stream_ptr()))
-        for c0, n, wq in chunks:
-            a = _abi.ConvArgs()
-            a.transposed, a.B, a.nsrc = 0, 1, 1
-            a.src[0] = frames.data_ptr()
-            a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, B, Q
-            a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.Ho, a.Wo = B, Q, n, 1, J, 1, 1, B, T
-            a.wq, a.bias, a.slope = wq.data_ptr(), None, 1.0
-            a.y_nchw = out.data_ptr() + 4 * c0 * T
-            a.y_cs, a.y_hs, a.y_ws = T, c2 * T, 1            # out[b=row, c0 + co, t]
-            _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+        c2, _, win = w.shape
+        pad = self.pad if self.center else 0
+        T = (L + 2 * pad - win) // self.hop_size + 1
+        out = torch.empty((B, c2, T), device=x.device, dtype=torch.float32)
+        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size) and B > 0
+        if self.engine == 'umma' and not tc:
+            raise RuntimeError(f'ConvSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
+        with torch.cuda.device(x.device), _abi.stage('stft'):
+            if tc:
+                _frames_project(x, self._cached('fwd', _frames_operand), self.hop_size, pad, T, out)
+            else:
+                _abi.check(_abi.lib().se_stft_fwd(_abi.ptr(x), B, L, _abi.ptr(w.contiguous()), c2, win, self.hop_size,
+                                                  self.pad, int(self.center), _abi.ptr(out), T, _abi.stream_ptr()))
+        return out
+
+    def _project_adjoint(self, g, L):
+        """d loss / d x from d loss / d spec [B, C2, T]."""
+        c2, _, win = self.weight.shape
+        hop = self.hop_size
+        if not _tc_ok(win, hop):
+            raise RuntimeError('ConvSTFT: backward needs the tensor-core framing (hop >= 8, ceil(win/hop) <= 16)')
+        B, _, T = g.shape
+        pad = self.pad if self.center else 0
+        full = (T - 1) * hop + win
+        gp = torch.zeros((B, L + 2 * pad), device=g.device, dtype=torch.float32)
+        with torch.cuda.device(g.device), _abi.stage('stft_bwd'):
+            buf = gp if full == gp.shape[1] else torch.empty((B, full), device=g.device, dtype=torch.float32)
+            _overlap_add(g, self._cached('adj', _ola_operand), hop, None, buf, 0, full)
+            if buf is not gp:
+                gp[:, :full] = buf
+        if pad == 0:
+            return gp
+        gx = gp[:, pad:pad + L].clone()
+        # adjoint of F.pad(mode='reflect') (conv_stft.py:60-62): the mirrored samples add onto their sources
+        gx[:, 1:pad + 1] += gp[:, :pad].flip(1)
+        gx[:, L - 1 - pad:L - 1] += gp[:, pad + L:].flip(1)
+        return gx
 
     def forward(self, inputs):
         x = _abi.require_cuda_f32(inputs, 'ConvSTFT.forward(inputs)')
-        _no_grad_only('ConvSTFT', x)
         if x.dim() == 1:
             x = x[None, :]
         elif x.dim() == 3:
@@ -127,7 +233,7 @@ class ConvSTFT(nn.Module):
         elif x.dim() != 2:
             raise RuntimeError(f'ConvSTFT: expected a 1-, 2- or 3-D tensor, got {x.dim()}-D')
         x = x.contiguous()
-        w = _abi.require_cuda_f32(self.weight, 'ConvSTFT.weight').contiguous()
+        w = _abi.require_cuda_f32(self.weight, 'ConvSTFT.weight')
         B, L = x.shape
         c2, _, win = w.shape
         pad = self.pad if self.center else 0
@@ -135,24 +241,22 @@ class ConvSTFT(nn.Module):
             raise RuntimeError(f'ConvSTFT: reflect padding ({pad}) must be smaller than the input length ({L})')
         if L + 2 * pad < win:
             raise RuntimeError(f'ConvSTFT: input length {L} is shorter than one window ({win})')
-        T = (L + 2 * pad - win) // self.hop_size + 1
-        out = torch.empty((B, c2, T), device=x.device, dtype=torch.float32)
-        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size) and B > 0
-        if self.engine == 'umma' and not tc:
-            raise RuntimeError(f'ConvSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
+        if torch.is_grad_enabled() and x.requires_grad:
+            out = _StftFn.apply(self, x)
+        else:
+            out = self._project(x)
+        if not self.return_mag_phase:
+            return out
+        F_ = self.fft_size // 2 + 1
+        if torch.is_grad_enabled() and out.requires_grad:
+            # CRN's polar branch under autograd (conv_stft.py:58-64): plain pointwise ops
+            real, imag = out[:, :F_], out[:, F_:]
+            return torch.sqrt(real ** 2 + imag ** 2), torch.atan2(imag, real)
+        T = out.shape[2]
+        mags = torch.empty((B, F_, T), device=x.device, dtype=torch.float32)
+        phase = torch.empty_like(mags)
         with torch.cuda.device(x.device), _abi.stage('stft'):
-            if tc:
-                self._forward_tc(x, w, out, T, pad)
-            else:
-                _abi.check(_abi.lib().se_stft_fwd(_abi.ptr(x), B, L, _abi.ptr(w), c2, win, self.hop_size,
-                                                  self.pad, int(self.center), _abi.ptr(out), T,
-                                                  _abi.stream_ptr()))
-            if not self.return_mag_phase:
-                return out
-            F = self.fft_size // 2 + 1
-            mags = torch.empty((B, F, T), device=x.device, dtype=torch.float32)
-            phase = torch.empty_like(mags)
-            _abi.check(_abi.lib().se_magphase_fwd(_abi.ptr(out), B, F, T, _abi.ptr(mags), _abi.ptr(phase),
+            _abi.check(_abi.lib().se_magphase_fwd(_abi.ptr(out), B, F_, T, _abi.ptr(mags), _abi.ptr(phase),
                                                   _abi.stream_ptr()))
         return mags, phase
 
@@ -172,26 +276,11 @@ class ConviSTFT(nn.Module):
         self.pad = self.fft_size // 2
         self._packed = None
         self._packed_key = None
-        self._tc = None
-        self._tc_key = None
         self._scale = {}
 
     engine = 'auto'
 
-    def _tc_operands(self, w):
-        """inverse basis as a 1 x J convolution over frames with 2F input channels and `hop` output
-        channels (one per hop phase): y[q*hop + r] = sum_j sum_c W[c, j*hop + r] * spec[c, q - j]
-        (the conv_transpose1d of conv_stft.py:99 regrouped by output phase)."""
-        key = (w.data_ptr(), w._version, w.device)
-        if self._tc_key != key:
-            c2, _, win = w.shape
-            hop = self.hop_size
-            J = -(-win // hop)
-            Cp = _round_up(c2, 64)
-            wp = F.pad(w[:, 0, :], (0, J * hop - win)).view(c2, J, hop).flip(1).permute(2, 0, 1).contiguous()
-            self._tc, self._tc_key = (J, Cp, _prep_wq(wp, hop, c2, J, Cp)), key
-            self._scale = {}
-        return self._tc
+    _cached = ConvSTFT._cached
 
     def _ola_scale(self, T, J):
         """1 / (sum of squared windows + 1e-8) per output sample (conv_stft.py:101-106), [Q*hop]."""
@@ -200,7 +289,7 @@ class ConviSTFT(nn.Module):
         sc = self._scale.get(key)
         if sc is None:
             hop, win = self.hop_size, self.window_size
-            w2 = F.pad(window.reshape(-1).double() ** 2, (0, J * hop - win)).view(J, hop)
+            w2 = F.pad(window.detach().reshape(-1).double() ** 2, (0, J * hop - win)).view(J, hop)
             coff = torch.zeros((T + J - 1, hop), device=window.device, dtype=torch.float64)
             for j in range(J):
                 coff[j:j + T] += w2[j]
@@ -208,25 +297,42 @@ class ConviSTFT(nn.Module):
             self._scale = {key: sc}
         return sc
 
-    def _forward_tc(self, spec, w, out, start, out_len):
-        B, c2, T = spec.shape
+    def _synthesize(self, spec, start, out_len):
+        """[B, C2, T] -> [B, out_len]: overlap-add, normaliser, crop -- tensor-core framing or SIMT kernel"""
+        w = self.weight
+        c2, _, win = w.shape
+        B, _, T = spec.shape
+        out = torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
+        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size)
+        if self.engine == 'umma' and not tc:
+            raise RuntimeError(f'ConviSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
+        with torch.cuda.device(spec.device), _abi.stage('istft'):
+            if tc:
+                operand = self._cached('fwd', _ola_operand)
+                _overlap_add(spec, operand, self.hop_size, self._ola_scale(T, operand[0]), out, start, out_len)
+            else:
+                packed = self._packed_basis()
+                window = self.window.reshape(-1).contiguous()
+                _abi.check(_abi.lib().se_istft_fwd(_abi.ptr(spec), None, _abi.ptr(packed), _abi.ptr(window), B, c2, T,
+                                                   win, self.hop_size, start, out_len, _abi.ptr(out),
+                                                   _abi.stream_ptr()))
+        return out
+
+    def _synthesize_adjoint(self, g, T, start):
+        """d loss / d spec [B, C2, T] from d loss / d wav [B, out_len]."""
+        c2, _, win = self.weight.shape
         hop = self.hop_size
-        J, Cp, wq = self._tc_operands(w)
-        scale = self._ola_scale(T, J)
-        img = torch.empty((1, 2, B, T, Cp), device=spec.device, dtype=torch.bfloat16)
-        _abi.check(_abi.lib().se_cl2_from_strided(_abi.ptr(spec), 0, T, c2 * T, 1, c2, B, T, _abi.ptr(img), Cp,
-                                                  _abi.stream_ptr()))
-        a = _abi.ConvArgs()
-        a.transposed, a.B, a.nsrc = 0, 1, 1
-        a.src[0] = img.data_ptr()
-        a.src_Cp[0], a.src_Hpitch[0], a.src_Wpitch[0] = Cp, B, T
-        a.H, a.W, a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw = B, T, hop, 1, J, 1, 1, 0, J - 1
-        a.Ho, a.Wo = B, T + J - 1
-        a.wq, a.bias, a.slope = wq.data_ptr(), None, 1.0
-        a.y_nchw = out.data_ptr()
-        a.y_cs, a.y_hs, a.y_ws, a.y_off, a.y_lim = 1, out_len, hop, -start, out_len
-        a.y_scale = scale.data_ptr()
-        _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+        if not _tc_ok(win, hop):
+            raise RuntimeError('ConviSTFT: backward needs the tensor-core framing (hop >= 8, ceil(win/hop) <= 16)')
+        B, out_len = g.shape
+        full = (T - 1) * hop + win
+        operand = self._cached('adj', _frames_operand)
+        gfull = torch.zeros((B, full), device=g.device, dtype=torch.float32)
+        gfull[:, start:start + out_len] = g * self._ola_scale(T, operand[0])[start:start + out_len]
+        out = torch.empty((B, c2, T), device=g.device, dtype=torch.float32)
+        with torch.cuda.device(g.device), _abi.stage('istft_bwd'):
+            _frames_project(gfull, operand, hop, 0, T, out)
+        return out
 
     def _packed_basis(self):
         """inverse basis regrouped per hop phase (se_istft_pack_basis); rebuilt when `weight` changes."""
@@ -244,18 +350,27 @@ class ConviSTFT(nn.Module):
     def forward(self, inputs, phase=None, output_length=None):
         """inputs: [B, N+2, T] complex spec, or [B, N//2+1, T] mags with `phase` (same shape)."""
         spec = _abi.require_cuda_f32(inputs, 'ConviSTFT.forward(inputs)')
-        _no_grad_only('ConviSTFT', spec, phase)
         if spec.dim() != 3:
             raise RuntimeError(f'ConviSTFT: expected [B, C, T], got {tuple(spec.shape)}')
         spec = spec.contiguous()
         w = _abi.require_cuda_f32(self.weight, 'ConviSTFT.weight')
         c2, _, win = w.shape
         B, C, T = spec.shape
+        needs_grad = torch.is_grad_enabled() and (spec.requires_grad or (phase is not None and phase.requires_grad))
         if phase is not None:
             phase = _abi.require_cuda_f32(phase, 'ConviSTFT.forward(phase)').contiguous()
             if phase.shape != spec.shape or 2 * C != c2:
                 raise RuntimeError(f'ConviSTFT: mags {tuple(spec.shape)} / phase {tuple(phase.shape)} '
                                    f'do not match a {c2}-row basis')
+            if needs_grad:
+                # polar branch under autograd (conv_stft.py:96-100): plain pointwise ops in front of the node
+                spec = torch.cat([spec * torch.cos(phase), spec * torch.sin(phase)], 1)
+            else:
+                rect = torch.empty((B, c2, T), device=spec.device, dtype=torch.float32)
+                with torch.cuda.device(spec.device), _abi.stage('istft'):
+                    _abi.check(_abi.lib().se_polar_to_rect(_abi.ptr(spec), _abi.ptr(phase), B, C, T, _abi.ptr(rect),
+                                                           _abi.stream_ptr()))
+                spec = rect
         elif C != c2:
             raise RuntimeError(f'ConviSTFT: expected {c2} spectrum rows, got {C}')
         full = (T - 1) * self.hop_size + win
@@ -267,25 +382,8 @@ class ConviSTFT(nn.Module):
         if output_length is not None:                    # conv_stft.py:113-114
             end = min(end, start + output_length)
         out_len = max(end - start, 0)
-        out = torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
         if out_len == 0 or B == 0:
-            return out
-        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size)
-        if self.engine == 'umma' and not tc:
-            raise RuntimeError(f'ConviSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
-        if tc:
-            with torch.cuda.device(spec.device), _abi.stage('istft'):
-                if phase is not None:
-                    rect = torch.empty((B, c2, T), device=spec.device, dtype=torch.float32)
-                    _abi.check(_abi.lib().se_polar_to_rect(_abi.ptr(spec), _abi.ptr(phase), B, C, T,
-                                                           _abi.ptr(rect), _abi.stream_ptr()))
-                    spec = rect
-                self._forward_tc(spec, w, out, start, out_len)
-            return out
-        with torch.cuda.device(spec.device), _abi.stage('istft'):
-            packed = self._packed_basis()
-            window = self.window.reshape(-1).contiguous()
-            _abi.check(_abi.lib().se_istft_fwd(_abi.ptr(spec), _abi.ptr(phase), _abi.ptr(packed),
-                                               _abi.ptr(window), B, c2, T, win, self.hop_size, start,
-                                               out_len, _abi.ptr(out), _abi.stream_ptr()))
-        return out
+            return torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
+        if needs_grad:
+            return _IstftFn.apply(self, spec, start, out_len)
+        return self._synthesize(spec, start, out_len)

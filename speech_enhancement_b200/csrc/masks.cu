@@ -100,6 +100,82 @@ int launch_mask(Plane nr, Plane ni, Plane mr, Plane mi, int64_t B, int F, int64_
   return SE_OK;
 }
 
+// ---- backward: (d re, d im) -> gradients of the four input planes, same strided inputs --------
+// Closed forms of what autograd derives from the reference's pointwise graph (file:line as in forward).
+template <int KIND>
+__device__ __forceinline__ void mask_grad(float nr, float ni, float mr, float mi, float gr, float gi,
+                                          float& dnr, float& dni, float& dmr, float& dmi) {
+  if (KIND == SE_MASK_DCCRN_R || KIND == SE_MASK_DCUNET_UNB) {
+    dnr = gr * mr; dmr = gr * nr; dni = gi * mi; dmi = gi * ni;
+  } else if (KIND == SE_MASK_DCCRN_C) {
+    dnr = gr * mr + gi * mi; dni = -gr * mi + gi * mr; dmr = gr * nr + gi * ni; dmi = -gr * ni + gi * nr;
+  } else if (KIND == SE_MASK_CARN) {
+    dnr = gr * mr - gi * mi; dni = -gr * mi + gi * mr; dmr = gr * nr + gi * ni; dmi = -gr * ni - gi * nr;
+  } else if (KIND == SE_MASK_DCUNET_SIGMOID) {
+    const float sr = 1.f / (1.f + expf(-mr)), si = 1.f / (1.f + expf(-mi));
+    dnr = gr * sr; dmr = gr * nr * sr * (1.f - sr); dni = gi * si; dmi = gi * ni * si * (1.f - si);
+  } else if (KIND == SE_MASK_FRCRN) {
+    const float tr = tanhf(mr), ti = tanhf(mi);
+    dnr = gr * tr; dmr = gr * nr * (1.f - tr * tr); dni = gi * ti; dmi = gi * ni * (1.f - ti * ti);
+  } else {
+    float n_mag, n_ph, m_mag, m_at;
+    mag_phase(nr, ni, n_mag, n_ph);
+    mag_phase(mr, mi, m_mag, m_at);
+    const float m_ph = KIND == SE_MASK_DCCRN_E ? atan2f(mi / m_mag, mr / m_mag) : m_at / m_mag;
+    const float th = tanhf(m_mag), A = n_mag * th;
+    float sn, cs;
+    sincosf(n_ph + m_ph, &sn, &cs);
+    const float dA = gr * cs + gi * sn, dth = A * (-gr * sn + gi * cs);
+    const float dn_mag = dA * th, dm_mag = dA * n_mag * (1.f - th * th);
+    const float n2 = nr * nr + ni * ni, m2 = mr * mr + mi * mi;
+    dnr = dn_mag * nr / n_mag - dth * ni / n2;
+    dni = dn_mag * ni / n_mag + dth * nr / n2;
+    if (KIND == SE_MASK_DCCRN_E) {
+      // atan2 of the normalised mask is scale invariant: d/dm = (-mi, mr) / (mr^2 + mi^2)
+      dmr = dm_mag * mr / m_mag - dth * mi / m2;
+      dmi = dm_mag * mi / m_mag + dth * mr / m2;
+    } else {
+      // phase = atan2(mi, mr) / |m|   (_1903_03107_dcunet.py:177)
+      const float k = m_at / (m_mag * m_mag * m_mag);
+      dmr = dm_mag * mr / m_mag + dth * (-mi / (m2 * m_mag) - k * mr);
+      dmi = dm_mag * mi / m_mag + dth * (mr / (m2 * m_mag) - k * mi);
+    }
+  }
+}
+
+// grid: (ceil(T / blockDim), rows = B*F); outputs contiguous: dn_* [B,F,T], dm_* [B,Fm,T]
+template <int KIND>
+__global__ void __launch_bounds__(128)
+mask_bwd_kernel(Plane nr, Plane ni, Plane mr, Plane mi, int F, int64_t T, const float* __restrict__ g,
+                float* __restrict__ dnr, float* __restrict__ dni, float* __restrict__ dmr, float* __restrict__ dmi) {
+  const int64_t row = blockIdx.y;
+  const int64_t b = row / F; const int f = (int)(row - b * F);
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const int Fm = KIND == SE_MASK_FRCRN ? F - 2 : F;
+  const int64_t on = (b * F + f) * T + t;
+  if (KIND == SE_MASK_FRCRN && f < 2) { dnr[on] = 0.f; dni[on] = 0.f; return; }
+  const int fm = KIND == SE_MASK_FRCRN ? f - 2 : f;
+  const float a = __ldg(nr.p + b * nr.bs + f * nr.fs + t), c = __ldg(ni.p + b * ni.bs + f * ni.fs + t);
+  const float d = __ldg(mr.p + b * mr.bs + fm * mr.fs + t), e = __ldg(mi.p + b * mi.bs + fm * mi.fs + t);
+  const float gr = __ldg(g + (b * 2 * F + f) * T + t), gi = __ldg(g + (b * 2 * F + F + f) * T + t);
+  float o0, o1, o2, o3;
+  mask_grad<KIND>(a, c, d, e, gr, gi, o0, o1, o2, o3);
+  dnr[on] = o0; dni[on] = o1;
+  const int64_t om = (b * Fm + fm) * T + t;
+  dmr[om] = o2; dmi[om] = o3;
+}
+
+template <int KIND>
+int launch_mask_bwd(Plane nr, Plane ni, Plane mr, Plane mi, int64_t B, int F, int64_t T, const float* g, float* dnr,
+                    float* dni, float* dmr, float* dmi, cudaStream_t s) {
+  const int64_t rows = B * F;
+  if (rows > 65535) return fail(SE_ERR_UNSUPPORTED, "se_mask_bwd: B*F > 65535 (split the batch)");
+  dim3 grid((unsigned)((T + 127) / 128), (unsigned)rows);
+  mask_bwd_kernel<KIND><<<grid, 128, 0, s>>>(nr, ni, mr, mi, F, T, g, dnr, dni, dmr, dmi);
+  return check_launch("se_mask_bwd");
+}
+
 }  // namespace se
 
 extern "C" int se_mask_fwd(int kind,
@@ -126,4 +202,33 @@ extern "C" int se_mask_fwd(int kind,
       return se::launch_mask<SE_MASK_FRCRN>(a, c, d, e, B, F, T, out, s);
   }
   return se::fail(SE_ERR_BAD_ARG, "se_mask_fwd: unknown kind %d", kind);
+}
+
+extern "C" int se_mask_bwd(int kind,
+                           const float* nr, int64_t nr_bs, int64_t nr_fs,
+                           const float* ni, int64_t ni_bs, int64_t ni_fs,
+                           const float* mr, int64_t mr_bs, int64_t mr_fs,
+                           const float* mi, int64_t mi_bs, int64_t mi_fs,
+                           int64_t B, int F, int64_t T, const float* grad_out, float* d_nr, float* d_ni,
+                           float* d_mr, float* d_mi, void* stream) {
+  SE_REQUIRE(nr && ni && mr && mi && grad_out && d_nr && d_ni && d_mr && d_mi, "se_mask_bwd: null pointer");
+  SE_REQUIRE(B >= 0 && F > 0 && T >= 0, "se_mask_bwd: bad dims");
+  if (B == 0 || T == 0) return SE_OK;
+  se::Plane a{nr, nr_bs, nr_fs}, c{ni, ni_bs, ni_fs}, d{mr, mr_bs, mr_fs}, e{mi, mi_bs, mi_fs};
+  cudaStream_t s = (cudaStream_t)stream;
+#define SE_BWD(K) return se::launch_mask_bwd<K>(a, c, d, e, B, F, T, grad_out, d_nr, d_ni, d_mr, d_mi, s)
+  switch (kind) {
+    case SE_MASK_DCCRN_R:        SE_BWD(SE_MASK_DCCRN_R);
+    case SE_MASK_DCCRN_C:        SE_BWD(SE_MASK_DCCRN_C);
+    case SE_MASK_DCCRN_E:        SE_BWD(SE_MASK_DCCRN_E);
+    case SE_MASK_DCUNET_UNB:     SE_BWD(SE_MASK_DCUNET_UNB);
+    case SE_MASK_DCUNET_SIGMOID: SE_BWD(SE_MASK_DCUNET_SIGMOID);
+    case SE_MASK_DCUNET_TANH:    SE_BWD(SE_MASK_DCUNET_TANH);
+    case SE_MASK_CARN:           SE_BWD(SE_MASK_CARN);
+    case SE_MASK_FRCRN:
+      SE_REQUIRE(F >= 3, "se_mask_bwd: FRCRN mask needs F >= 3");
+      SE_BWD(SE_MASK_FRCRN);
+  }
+#undef SE_BWD
+  return se::fail(SE_ERR_BAD_ARG, "se_mask_bwd: unknown kind %d", kind);
 }

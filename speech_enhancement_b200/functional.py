@@ -24,16 +24,8 @@ def _plane(t, name, B, F, T):
     return t
 
 
-def _mask(kind, nr, ni, mr, mi, mask_rows=None):
-    nr = _abi.require_cuda_f32(nr, 'noisy_real')
-    if nr.dim() != 3:
-        raise RuntimeError(f'noisy_real: expected [B, F, T], got {tuple(nr.shape)}')
-    if torch.is_grad_enabled() and any(t.requires_grad for t in (nr, ni, mr, mi)):
-        raise RuntimeError('mask ops: backward is not implemented in this build; use torch.no_grad()')
+def _mask_launch(kind, nr, ni, mr, mi):
     B, F, T = nr.shape
-    Fm = F if mask_rows is None else mask_rows
-    nr, ni = _plane(nr, 'noisy_real', B, F, T), _plane(ni, 'noisy_imag', B, F, T)
-    mr, mi = _plane(mr, 'mask_real', B, Fm, T), _plane(mi, 'mask_imag', B, Fm, T)
     out = torch.empty((B, 2 * F, T), device=nr.device, dtype=torch.float32)
     args = []
     for t in (nr, ni, mr, mi):
@@ -41,6 +33,44 @@ def _mask(kind, nr, ni, mr, mi, mask_rows=None):
     with torch.cuda.device(nr.device), _abi.stage('mask'):
         _abi.check(_abi.lib().se_mask_fwd(kind, *args, B, F, T, _abi.ptr(out), _abi.stream_ptr()))
     return out
+
+
+class _MaskFn(torch.autograd.Function):
+    """se_mask_fwd / se_mask_bwd as one autograd node (the reference builds ~24 pointwise nodes)."""
+
+    @staticmethod
+    def forward(ctx, kind, nr, ni, mr, mi):
+        ctx.kind = kind
+        ctx.save_for_backward(nr, ni, mr, mi)
+        return _mask_launch(kind, nr, ni, mr, mi)
+
+    @staticmethod
+    def backward(ctx, g):
+        nr, ni, mr, mi = ctx.saved_tensors
+        B, F, T = nr.shape
+        g = g.contiguous().float()
+        d_nr, d_ni = torch.empty((B, F, T), device=g.device), torch.empty((B, F, T), device=g.device)
+        d_mr, d_mi = torch.empty(mr.shape, device=g.device), torch.empty(mr.shape, device=g.device)
+        args = []
+        for t in (nr, ni, mr, mi):
+            args += [_abi.ptr(t), t.stride(0), t.stride(1)]
+        with torch.cuda.device(g.device), _abi.stage('mask_bwd'):
+            _abi.check(_abi.lib().se_mask_bwd(ctx.kind, *args, B, F, T, _abi.ptr(g), _abi.ptr(d_nr), _abi.ptr(d_ni),
+                                              _abi.ptr(d_mr), _abi.ptr(d_mi), _abi.stream_ptr()))
+        return None, d_nr, d_ni, d_mr, d_mi
+
+
+def _mask(kind, nr, ni, mr, mi, mask_rows=None):
+    nr = _abi.require_cuda_f32(nr, 'noisy_real')
+    if nr.dim() != 3:
+        raise RuntimeError(f'noisy_real: expected [B, F, T], got {tuple(nr.shape)}')
+    B, F, T = nr.shape
+    Fm = F if mask_rows is None else mask_rows
+    nr, ni = _plane(nr, 'noisy_real', B, F, T), _plane(ni, 'noisy_imag', B, F, T)
+    mr, mi = _plane(mr, 'mask_real', B, Fm, T), _plane(mi, 'mask_imag', B, Fm, T)
+    if torch.is_grad_enabled() and any(t.requires_grad for t in (nr, ni, mr, mi)):
+        return _MaskFn.apply(kind, nr, ni, mr, mi)
+    return _mask_launch(kind, nr, ni, mr, mi)
 
 
 def mask_dccrn(masking, noisy_real, noisy_imag, mask_real, mask_imag):

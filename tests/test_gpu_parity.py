@@ -396,3 +396,102 @@ def test_complex_linear_tensor_engine(M, cin, cout):
         m.engine = 'torch'
         y_t = m(x.to(DEV))
     assert y.shape == ref.shape and rel_l2(y.cpu(), ref) < 3e-5 and rel_l2(y_t.cpu(), ref) < TOL_EXACT
+
+
+# ----------------------------------------------------------------------------------- autograd
+def _grads(fn, inputs, seed):
+    """d/d inputs of sum(fn(*inputs) * fixed random weights)"""
+    inputs = [t.clone().requires_grad_(True) for t in inputs]
+    out = fn(*inputs)
+    outs = out if isinstance(out, (tuple, list)) else [out]
+    loss = 0
+    for i, o in enumerate(outs):
+        w = rand(tuple(o.shape), seed + i).to(o.device)
+        loss = loss + (o * w).sum()
+    loss.backward()
+    return [t.grad.detach().cpu() for t in inputs], [o.detach().cpu() for o in outs]
+
+
+@pytest.mark.parametrize('win,hop,fft,L,center', [(400, 100, 512, 4000, True), (512, 128, 512, 4096, True),
+                                                  (320, 160, 640, 3200, True), (320, 160, 512, 3360, True),
+                                                  (400, 100, 512, 3000, False)])
+def test_stft_istft_backward_vs_oracle(win, hop, fft, L, center):
+    """the autograd nodes of ConvSTFT / ConviSTFT (adjoint GEMMs on the conv engine) against torch autograd of
+    the CPU oracle (= the reference's F.conv1d / conv_transpose1d graph)."""
+    x = rand((3, L), 50, 0.1)
+    st, ist = se.ConvSTFT(win, hop, fft, center=center).to(DEV), se.ConviSTFT(win, hop, fft, center=center).to(DEV)
+    st_o, ist_o = OPS.ConvSTFT(win, hop, fft, center=center), OPS.ConviSTFT(win, hop, fft, center=center)
+    (gx,), (spec,) = _grads(st, [x.to(DEV)], 60)
+    (gx_o,), (spec_o,) = _grads(st_o, [x], 60)
+    assert rel_l2(spec, spec_o) < 3e-5 and rel_l2(gx, gx_o) < 3e-5
+    (gs,), (wav,) = _grads(ist, [spec_o.to(DEV)], 70)
+    (gs_o,), (wav_o,) = _grads(ist_o, [spec_o], 70)
+    assert wav.shape == wav_o.shape and rel_l2(gs, gs_o) < 3e-5
+    (gs2,), _ = _grads(lambda s_: ist(s_, output_length=L - 7), [spec_o.to(DEV)], 71)
+    (gs2_o,), _ = _grads(lambda s_: ist_o(s_, output_length=L - 7), [spec_o], 71)
+    assert rel_l2(gs2, gs2_o) < 3e-5
+    # polar branches (CRN): mags/phase out of the STFT and into the iSTFT
+    stp, stp_o = se.ConvSTFT(win, hop, fft, center=center, return_mag_phase=True).to(DEV), \
+        OPS.ConvSTFT(win, hop, fft, center=center, return_mag_phase=True)
+    (gp,), _ = _grads(lambda x_: stp(x_)[0], [x.to(DEV)], 80)
+    (gp_o,), _ = _grads(lambda x_: stp_o(x_)[0], [x], 80)
+    assert rel_l2(gp, gp_o) < 1e-4
+    mags, ph = rand((2, fft // 2 + 1, 9), 81).abs() + 0.1, rand((2, fft // 2 + 1, 9), 82)
+    g_mp, _ = _grads(lambda m_, p_: ist(m_, p_), [mags.to(DEV), ph.to(DEV)], 83)
+    g_mp_o, _ = _grads(lambda m_, p_: ist_o(m_, p_), [mags, ph], 83)
+    assert rel_l2(g_mp[0], g_mp_o[0]) < 3e-5 and rel_l2(g_mp[1], g_mp_o[1]) < 3e-5
+
+
+def test_mask_backward_all_kinds_vs_oracle():
+    """se_mask_bwd against torch autograd of the oracle's pointwise graph, strided inputs included."""
+    B, F_, T = 2, 33, 41
+    nr, ni, mr, mi = (rand((B, F_, T), 90 + i) for i in range(4))
+    cases = [(lambda *a, m=m: SF.mask_dccrn(m, *a), lambda *a, m=m: OPS.mask_dccrn(m, *a)) for m in 'RCE']
+    cases += [(lambda *a, m=m: SF.mask_dcunet(m, *a), lambda *a, m=m: OPS.mask_dcunet(m, *a))
+              for m in ('unbounded', 'bounded_sigmoid', 'bounded_tanh')]
+    cases += [(SF.mask_carn, OPS.mask_carn)]
+    for ours, ref in cases:
+        g, (o,) = _grads(ours, [t.to(DEV) for t in (nr, ni, mr, mi)], 95)
+        g_o, (o_o,) = _grads(ref, [nr, ni, mr, mi], 95)
+        assert rel_l2(o, o_o) < TOL_EXACT
+        for a, b in zip(g, g_o):
+            assert rel_l2(a, b) < 2e-5
+    g, _ = _grads(SF.mask_frcrn, [nr.to(DEV), ni.to(DEV), mr[:, 2:].to(DEV), mi[:, 2:].to(DEV)], 96)
+    g_o, _ = _grads(OPS.mask_frcrn, [nr, ni, mr[:, 2:].contiguous(), mi[:, 2:].contiguous()], 96)
+    for a, b in zip(g, g_o):
+        assert rel_l2(a, b) < 2e-5
+    # planes that are slices of a bigger tensor (as in the models): grads flow back to the parent
+    spec = rand((B, 2 * F_, T), 97).to(DEV).requires_grad_(True)
+    net = rand((B, 2, F_, T), 98).to(DEV).requires_grad_(True)
+    SF.mask_carn(spec[:, :F_], spec[:, F_:], net[:, 0], net[:, 1]).square().sum().backward()
+    spec_c, net_c = spec.detach().cpu().requires_grad_(True), net.detach().cpu().requires_grad_(True)
+    OPS.mask_carn(spec_c[:, :F_], spec_c[:, F_:], net_c[:, 0], net_c[:, 1]).square().sum().backward()
+    assert rel_l2(spec.grad.cpu(), spec_c.grad) < 2e-5 and rel_l2(net.grad.cpu(), net_c.grad) < 2e-5
+
+
+def test_carn_train_step_matches_cpu_oracle():
+    """BASELINE config 4 at small size: two AdamW steps of CARN (STFT / mask / iSTFT autograd nodes of this
+    package around stock real convolutions) against the same steps on the CPU oracle."""
+    from speech_enhancement_b200 import training
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        ref = callers.CARN(ops=OPS).train()
+        sd = seeded_state_dict(ref, seed=8)
+        ref.load_state_dict(sd)
+        ours = callers.CARN().train()
+        ours.load_state_dict(sd)
+        ours.to(DEV)
+        mix, clean = synth_noisy_speech(2, 8000, seed=30), synth_noisy_speech(2, 8000, seed=31)
+        o_ref, o_ours = training.make_optimizer(ref), training.make_optimizer(ours)
+        f_ref, f_ours = training.FlatGradients(ref), training.FlatGradients(ours)
+        for step in range(2):
+            l_ref = training.train_step(ref, o_ref, f_ref, mix, clean)
+            l_ours = training.train_step(ours, o_ours, f_ours, mix.to(DEV), clean.to(DEV))
+            assert abs(l_ref.item() - l_ours.item()) < 2e-3 * max(1.0, abs(l_ref.item()))
+            assert rel_l2(f_ours.buffer.cpu(), f_ref.buffer) < 2e-3
+        for (k, a), (_, b) in zip(ours.state_dict().items(), ref.state_dict().items()):
+            if a.dtype.is_floating_point:
+                assert rel_l2(a.cpu(), b) < 2e-3, k
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
