@@ -43,6 +43,10 @@ MODELS = {
     'frcrn': dict(cls='FRCRN', args=(320, 160, 640), stft=(320, 160, 640), conv_gflop=97.61,
                   name='FRCRN', metric='frcrn_audio_seconds_enhanced_per_second', act_mb=500),
 }
+# BASELINE configs[3]: CARN forward+backward+AdamW, GLOBAL batch 32 split over the GPUs (strong scaling),
+# one flat-gradient allreduce per step (speech_enhancement_b200/training.py)
+MODELS['carn_train'] = dict(cls='CARN', args=(320, 160, 512), stft=(320, 160, 512), conv_gflop=0.0, train=True,
+                            name='CARN training step', metric='carn_train_audio_seconds_per_second', act_mb=0)
 MODEL = MODELS['dccrn']
 
 
@@ -184,6 +188,150 @@ class StageTimer:
     def totals_ms(self):
         torch.cuda.synchronize()
         return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self.events.items()}
+
+
+def time_cpu_train(batch, iters):
+    """CARN step on the CPU oracle (B_cpu = 4), all host threads"""
+    from speech_enhancement_b200 import training
+    from speech_enhancement_b200.synth import synth_noisy_speech
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1)
+    torch.set_num_threads(cores)
+    torch.set_flush_denormal(True)
+    model = build_oracle().train()
+    opt, flat = training.make_optimizer(model), training.FlatGradients(model)
+    mix, clean = synth_noisy_speech(batch, L, seed=1), synth_noisy_speech(batch, L, seed=2)
+    training.train_step(model, opt, flat, mix, clean, reduce=False)
+    ts = []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        training.train_step(model, opt, flat, mix, clean, reduce=False)
+        ts.append(time.perf_counter() - t0)
+    ts.sort()
+    med = ts[len(ts) // 2]
+    return batch * CLIP_S / med, torch.get_num_threads(), med
+
+
+def run_train(args):
+    """--model carn_train: one data-parallel training step per bench step."""
+    import torch.distributed as dist
+    from speech_enhancement_b200 import _abi, sharding, training
+    from speech_enhancement_b200.synth import synth_noisy_speech
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    GB = 32                                                     # global batch of configs[3]
+    if args.impl == 'reference':
+        if rank == 0:
+            value, cores, sec = time_cpu_train(4, max(args.steps, 1))
+            print(json.dumps({'impl': 'reference', 'metric': MODEL['metric'], 'value': value, 'unit': UNIT,
+                              'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3,
+                              'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32',
+                              'data': 'synthetic', 'config': {'workload': 'CARN fwd+bwd+AdamW step', 'global_batch': GB},
+                              'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                                               'sample': '4 x 4 s utterances per step on the CPU oracle'},
+                              'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+                              'gpu_launches': 0}), flush=True)
+        return
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py: no CUDA device (speech_enhancement_b200 has no CPU path)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    torch.backends.cudnn.allow_tf32 = False                     # fp32 math in the stock convolutions too
+    lib = _abi.lib()
+    model = build_models(dev).train()
+    opt, flat = training.make_optimizer(model), training.FlatGradients(model)
+    b0, b1 = sharding.shard_bounds(GB, rank, world)
+    host = [(synth_noisy_speech(GB, L, seed=200 + i)[b0:b1].pin_memory(),
+             synth_noisy_speech(GB, L, seed=300 + i)[b0:b1].pin_memory()) for i in range(3)]
+    dev_in = [(m.to(dev), c.to(dev)) for m, c in host]
+
+    def step(i):
+        return training.train_step(model, opt, flat, *dev_in[i % 3])
+
+    def step_e2e(i):
+        m, c = host[i % 3]
+        loss = training.train_step(model, opt, flat, m.to(dev, non_blocking=True), c.to(dev, non_blocking=True))
+        return loss.item()                                      # D2H of the step's result
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        return sharding.reduce_max(e0.elapsed_time(e1), device=dev)
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = lib.se_launch_count()
+    ms = timed(step, args.steps)
+    launches = lib.se_launch_count() - n0
+    step_e2e(0)
+    ms_e2e = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    # per-stage profiling pass: EVERY rank steps (the step contains the allreduce), only rank 0 records
+    st = StageTimer() if rank == 0 else None
+    nprof = min(args.steps, 3)
+    for i in range(nprof):
+        step(i)
+    barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    tot = st.totals_ms()
+    st.close()
+    win, hop, fft = MODEL['stft']
+    T = (L + fft - win) // hop + 1
+    nb = b1 - b0
+    alg = {'stft': 4 * (L + (fft + 2) * T), 'istft': 4 * ((fft + 2) * T + L), 'mask': 4 * 6 * (fft // 2 + 1) * T}
+    alg.update(stft_bwd=alg['stft'], istft_bwd=alg['istft'], mask_bwd=4 * 10 * (fft // 2 + 1) * T)
+    stages = {}
+    for k, byt in alg.items():
+        t = tot.get(k, 0.0) / nprof / 1e3
+        stages[k] = {'ms': t * 1e3, 'GB/s': byt * nb / t / 1e9 if t else None,
+                     'frac_hbm': byt * nb / t / 1e9 / pk['hbm_gbs'] if t else None}
+    hot = sum(v['ms'] for v in stages.values())
+    stages['step_ms'] = ms / args.steps
+    stages['hot_path_share'] = hot / (ms / args.steps)
+    dom = max(alg, key=lambda k: stages[k]['ms'])
+    roofline = {'bound': 'hbm', 'kernel': f'{dom} (largest of this package\'s kernels in the step; the real convolutions '
+                                          'and the LSTM of CARN are stock cuDNN, out of scope)',
+                'achieved': stages[dom]['GB/s'], 'peak': pk['hbm_gbs'], 'unit': 'GB/s',
+                'frac': stages[dom]['frac_hbm'], 'traffic': None, 'peak_source': pk['source'] + ' HBM copy'}
+    audio_s = GB * CLIP_S * args.steps
+    cpu_val, cores, cpu_sec = time_cpu_train(4, 1)
+    grad_bytes = flat.buffer.numel() * 4
+    line = {'metric': MODEL['metric'], 'value': audio_s / (ms / 1e3), 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'strong',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'CARN (320/160/512, lstm 512) forward + SI-SNR + backward + clip 0.5 + AdamW, global '
+                                   f'batch {GB} x 4 s split {nb} per GPU, one flat-gradient allreduce '
+                                   f'({grad_bytes / 1e6:.1f} MB) per step', 'global_batch': GB, 'per_gpu_batch': nb,
+                       'parallelism': f'data-parallel x{world}, NCCL allreduce of the flat gradient',
+                       'l2_policy': 'inputs rotate over 3 buffers; activations exceed L2'},
+            'e2e': {'value': audio_s / (ms_e2e / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': 2 * nb * L * 4 * world,
+                    'd2h_bytes_per_step': 4 * world, 'ms_per_step': ms_e2e / args.steps},
+            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'stages': stages,
+            'cpu_baseline': {'value': cpu_val, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                             'sample': f'one CARN step at 4 x 4 s on the CPU oracle ({cpu_sec:.2f} s)'}}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_ours(args):
@@ -328,6 +476,8 @@ def main():
     args = ap.parse_args()
     global MODEL
     MODEL = MODELS[args.model]
+    if MODEL.get('train'):
+        return run_train(args)
     if args.impl == 'reference':
         run_reference(args)
     else:

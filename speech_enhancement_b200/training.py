@@ -69,15 +69,16 @@ def make_optimizer(model, lr=1e-3, weight_decay=1e-2):
     return torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=weight_decay)
 
 
-def train_step(model, optimizer, flat, mix, clean, clip_norm=0.5):
+def train_step(model, optimizer, flat, mix, clean, clip_norm=0.5, reduce=True):
     """one data-parallel step on this rank's shard; returns the local loss (python float is NOT taken here:
-    no host sync inside the step)."""
+    no host sync inside the step).  reduce=False skips the allreduce (single-replica timing legs)."""
     flat.rebind()
     flat.zero()
     _, wav = model(mix)
     loss = si_snr_loss(pad_or_truncate(wav, clean), clean)
     loss.backward()
-    flat.allreduce_mean()
+    if reduce:
+        flat.allreduce_mean()
     if clip_norm:
         torch.nn.utils.clip_grad_norm_(flat.params, clip_norm)
     optimizer.step()
