@@ -174,6 +174,22 @@ SE_API int se_cconvT_col2im(const float* P, int64_t B, int H, int W, int Np, int
                             int sw, int ph, int pw, int Ho, int Wo, const float* bias, float slope, float* y,
                             void* stream);
 
+/* ---- weight gradient of the packed complex convolution (autograd of complex_nn.py:52-91) -------------
+ * Activations are staged as NC2: NCHW bf16 hi|lo planes [B][2][C][H][Wp], Wp = W rounded up to 8.
+ *   G[tap][cu][cv] += sum_{b,hu,wu} U[b,cu,hu,wu] * V[b,cv, hu*sh + dh - ph, wu*sw + dw - pw]
+ * conv : U = dY, V = X  ->  d packed[co][ci][tap] = G[tap][co][ci]
+ * convT: U = X,  V = dY ->  d packed[co][ci][tap] = G[tap][ci][co]
+ * U is staged with se_nc2_from_nchw; V with se_nc2_gather_w, one copy per kernel column dw already sampled
+ * on U's column grid (TMA needs a 16-byte aligned innermost start, so the column shift cannot be a box
+ * coordinate).  G (fp32, [kh*kw][Cu][Cv]) must be zeroed by the caller; partial sums are added atomically. */
+SE_API int64_t se_nc2_elems(int64_t B, int C, int H, int W);
+SE_API int se_nc2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* nc2, void* stream);
+SE_API int64_t se_nc2_gather_elems(int64_t B, int C, int H, int Wu, int kw);
+SE_API int se_nc2_gather_w(const float* x, int64_t B, int C, int H, int W, int Wu, int kw, int sw, int pw, void* out,
+                           void* stream);
+SE_API int se_cconv_wgrad(const void* u_nc2, int Cu, int Hu, int Wu, const void* v_gather, int Cv, int Hv,
+                          int64_t B, int kh, int kw, int sh, int ph, float* G, void* stream);
+
 /* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
  * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),
  * so slices of the STFT output and of the decoder output are consumed in place.  For

@@ -47,6 +47,11 @@ _SIGS = {
     'se_lstm_rec_pair_fwd': (C.c_int, [_P, _L, _P, _P, _L, _L, _I, _P, _P, _P]),
     'se_cl2_from_rows': (C.c_int, [_P, _L, _I, _L, _P, _I, _P]),
     'se_cconvT_col2im': (C.c_int, [_P, _L] + [_I] * 12 + [_P, C.c_float, _P, _P]),
+    'se_nc2_elems': (C.c_int64, [_L, _I, _I, _I]),
+    'se_nc2_from_nchw': (C.c_int, [_P, _L, _I, _I, _I, _P, _P]),
+    'se_nc2_gather_elems': (C.c_int64, [_L, _I, _I, _I, _I]),
+    'se_nc2_gather_w': (C.c_int, [_P, _L, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'se_cconv_wgrad': (C.c_int, [_P, _I, _I, _I, _P, _I, _I, _L, _I, _I, _I, _I, _P, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_mask_bwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P, _P, _P, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),

@@ -104,43 +104,122 @@ class ComplexConv(nn.Module):
         yr, yi = torch.chunk(y, 2, dim=1)
         return merge_real_imag(x, yr, yi)
 
+    def _geometry(self):
+        rc = self.real_conv
+        return _pair(rc.stride) + _pair(rc.padding)
+
+    def _launch(self, transposed, x, packed, bias, cout2, kh, kw, Ho, Wo):
+        """one engine call: NCHW fp32 in / out, `packed` [cout2][cin2*kh*kw] in the engine's layout"""
+        B, c2, H, W = x.shape
+        sh, sw, ph, pw = self._geometry()
+        lib = _abi.lib()
+        fn = lib.se_cconvT2d_fwd if transposed else lib.se_cconv2d_fwd
+        y = torch.empty((B, cout2, Ho, Wo), device=x.device, dtype=torch.float32)
+        ws_bytes = lib.se_cconv_workspace_bytes(B, c2, H, W, cout2, kh, kw, sh, sw,
+                                                int(transposed)) if self.engine != _abi.ENGINE_SIMT else 0
+        ws = torch.empty((ws_bytes,), device=x.device, dtype=torch.uint8) if ws_bytes > 0 else None
+        _abi.check(fn(_abi.ptr(x), _abi.ptr(packed), _abi.ptr(bias), B, c2, H, W, cout2, kh, kw,
+                      sh, sw, ph, pw, _abi.ptr(y), Ho, Wo, self.engine, _abi.ptr(ws), ws_bytes, _abi.stream_ptr()))
+        return y
+
+    def _out_size(self, H, W, kh, kw):
+        sh, sw, ph, pw = self._geometry()
+        if self._transposed:
+            oph, opw = _pair(self.real_conv.output_padding)
+            return (H - 1) * sh - 2 * ph + kh + oph, (W - 1) * sw - 2 * pw + kw + opw
+        return (H + 2 * ph - kh) // sh + 1, (W + 2 * pw - kw) // sw + 1
+
     def _forward_stacked(self, x):
         x = _abi.require_cuda_f32(x, f'{type(self).__name__}.forward(x)')
-        if torch.is_grad_enabled() and (x.requires_grad or self.real_conv.weight.requires_grad):
-            raise RuntimeError(f'{type(self).__name__}: backward is not implemented in this build; '
-                               'call under torch.no_grad()')
         if x.dim() != 4:
             raise RuntimeError(f'{type(self).__name__}: expected [B, C, H, W], got {tuple(x.shape)}')
         self._check_supported()
         x = x.contiguous()
+        rc, ic = self.real_conv, self.imag_conv
+        if torch.is_grad_enabled() and (x.requires_grad or rc.weight.requires_grad or ic.weight.requires_grad):
+            return _CConvFn.apply(self, x, rc.weight, ic.weight, rc.bias, ic.bias)
+        return self._forward_impl(x)
+
+    def _forward_impl(self, x):
         with torch.cuda.device(x.device), _abi.stage('cconv'):
             packed, bias, co, ci, kh, kw = self._packed()
             B, c2, H, W = x.shape
             if c2 != 2 * ci:
                 raise RuntimeError(f'{type(self).__name__}: expected {2 * ci} input channels, got {c2}')
-            rc = self.real_conv
-            sh, sw = _pair(rc.stride)
-            ph, pw = _pair(rc.padding)
-            lib = _abi.lib()
-            if self._transposed:
-                oph, opw = _pair(rc.output_padding)
-                Ho = (H - 1) * sh - 2 * ph + kh + oph
-                Wo = (W - 1) * sw - 2 * pw + kw + opw
-                fn = lib.se_cconvT2d_fwd
-            else:
-                Ho = (H + 2 * ph - kh) // sh + 1
-                Wo = (W + 2 * pw - kw) // sw + 1
-                fn = lib.se_cconv2d_fwd
+            Ho, Wo = self._out_size(H, W, kh, kw)
             if Ho <= 0 or Wo <= 0:
                 raise RuntimeError(f'{type(self).__name__}: input {tuple(x.shape)} too small for the kernel')
-            y = torch.empty((B, 2 * co, Ho, Wo), device=x.device, dtype=torch.float32)
-            ws_bytes = lib.se_cconv_workspace_bytes(B, c2, H, W, 2 * co, kh, kw, sh, sw,
-                                                    int(self._transposed)) if self.engine != _abi.ENGINE_SIMT else 0
-            ws = torch.empty((ws_bytes,), device=x.device, dtype=torch.uint8) if ws_bytes > 0 else None
-            _abi.check(fn(_abi.ptr(x), _abi.ptr(packed), _abi.ptr(bias), B, c2, H, W, 2 * co, kh, kw,
-                          sh, sw, ph, pw, _abi.ptr(y), Ho, Wo, self.engine, _abi.ptr(ws), ws_bytes,
-                          _abi.stream_ptr()))
-        return y
+            return self._launch(self._transposed, x, packed, bias, 2 * co, kh, kw, Ho, Wo)
+
+    # ---- backward pieces (autograd of complex_nn.py:52-65; the reference gets them from ATen) ----------
+    def _dgrad(self, gy, x_shape):
+        """d loss / d x: the adjoint convolution = the OTHER flavour of the engine with the packed weight's
+        channel axes swapped (no tap flip: the engine's transposed form indexes taps like PyTorch's)."""
+        packed, _, co, ci, kh, kw = self._packed()
+        key = self._pack_key
+        if self.__dict__.get('_pack_T_key') != key:
+            pt = packed.view(2 * co, 2 * ci, kh * kw).permute(1, 0, 2).contiguous().view(2 * ci, -1)
+            self.__dict__['_pack_T'], self.__dict__['_pack_T_key'] = pt, key
+        with torch.cuda.device(gy.device), _abi.stage('cconv_dgrad'):
+            return self._launch(not self._transposed, gy, self.__dict__['_pack_T'], None, 2 * ci, kh, kw,
+                                x_shape[2], x_shape[3])
+
+    def _wgrad(self, x, gy):
+        """d loss / d (packed weight) [2co][2ci][taps] through se_cconv_wgrad (pixel-reduction GEMM)."""
+        _, _, co, ci, kh, kw = self._packed()
+        sh, sw, ph, pw = self._geometry()
+        lib = _abi.lib()
+        u, v = (x, gy) if self._transposed else (gy, x)       # u: un-shifted grid, v: sampled through the taps
+        B = x.shape[0]
+        with torch.cuda.device(x.device), _abi.stage('cconv_wgrad'):
+            Cu, Hu, Wu = u.shape[1:]
+            Cv, Hv, Wv = v.shape[1:]
+            ub = torch.empty(lib.se_nc2_elems(B, Cu, Hu, Wu), device=x.device, dtype=torch.bfloat16)
+            _abi.check(lib.se_nc2_from_nchw(_abi.ptr(u), B, Cu, Hu, Wu, _abi.ptr(ub), _abi.stream_ptr()))
+            vb = torch.empty(lib.se_nc2_gather_elems(B, Cv, Hv, Wu, kw), device=x.device, dtype=torch.bfloat16)
+            _abi.check(lib.se_nc2_gather_w(_abi.ptr(v), B, Cv, Hv, Wv, Wu, kw, sw, pw, _abi.ptr(vb), _abi.stream_ptr()))
+            G = torch.zeros((kh * kw, Cu, Cv), device=x.device, dtype=torch.float32)
+            _abi.check(lib.se_cconv_wgrad(_abi.ptr(ub), Cu, Hu, Wu, _abi.ptr(vb), Cv, Hv, B, kh, kw, sh, ph, _abi.ptr(G),
+                                          _abi.stream_ptr()))
+        # G[tap][cu][cv] -> engine layout [2co][2ci][tap]
+        return G.permute(2, 1, 0) if self._transposed else G.permute(1, 2, 0)
+
+    def _unpack_grads(self, dP):
+        """gradient of the packed operand [[Wr, -Wi], [Wi, Wr]] -> (d real_conv.weight, d imag_conv.weight)"""
+        _, _, co, ci, kh, kw = self._packed()
+        dP = dP.reshape(2 * co, 2 * ci, kh, kw)
+        d_wr = dP[:co, :ci] + dP[co:, ci:]
+        d_wi = dP[co:, :ci] - dP[:co, ci:]
+        if self._transposed:                                  # module layout is [ci][co][kh][kw]
+            d_wr, d_wi = d_wr.transpose(0, 1), d_wi.transpose(0, 1)
+        return d_wr.contiguous(), d_wi.contiguous()
+
+
+class _CConvFn(torch.autograd.Function):
+    """ComplexConv2d / ComplexConvTranspose2d as ONE autograd node: forward, dgrad and wgrad each one
+    tensor-core launch on the packed real operand."""
+
+    @staticmethod
+    def forward(ctx, mod, x, wr, wi, br, bi):
+        ctx.mod = mod
+        ctx.save_for_backward(x)
+        return mod._forward_impl(x)
+
+    @staticmethod
+    def backward(ctx, gy):
+        mod = ctx.mod
+        (x,) = ctx.saved_tensors
+        gy = gy.contiguous().float()
+        need = ctx.needs_input_grad
+        dx = mod._dgrad(gy, x.shape) if need[1] else None
+        d_wr = d_wi = d_br = d_bi = None
+        if need[2] or need[3]:
+            d_wr, d_wi = mod._unpack_grads(mod._wgrad(x, gy))
+        if need[4] or need[5]:
+            co = gy.shape[1] // 2
+            s = gy.sum(dim=(0, 2, 3))
+            d_br, d_bi = s[:co] + s[co:], s[co:] - s[:co]     # packed bias = [br - bi, br + bi]
+        return None, dx, d_wr, d_wi, d_br, d_bi
 
 
 def _halve(in_channels, out_channels):

@@ -495,3 +495,53 @@ def test_carn_train_step_matches_cpu_oracle():
                 assert rel_l2(a.cpu(), b) < 2e-3, k
     finally:
         torch.backends.cudnn.allow_tf32 = tf32
+
+
+@pytest.mark.parametrize('i', range(len(CONV_CASES)))
+def test_cconv_backward_vs_oracle(i):
+    """autograd of ComplexConv2d / ComplexConvTranspose2d (dgrad on the engine with swapped weight axes, wgrad
+    on the pixel-reduction GEMM se_cconv_wgrad) against torch autograd of the oracle's four real convolutions."""
+    name, transposed, cin, cout, k, kw, H, W, B = CONV_CASES[i]
+    kw = dict(kw)
+    kw.setdefault('bias', i % 2 == 0)
+    mk = (lambda ns: ns.ComplexConvTranspose2d if transposed else ns.ComplexConv2d)
+    ours, ref = mk(se)(cin, cout, k, **kw), mk(OPS)(cin, cout, k, **kw)
+    sd = {key: rand(v.shape, 6000 + 10 * i + j, 0.2) for j, (key, v) in enumerate(sorted(ref.state_dict().items()))}
+    ours.load_state_dict(sd)
+    ref.load_state_dict(sd)
+    ours.to(DEV)
+    x = rand((B, cin, H, W), 7000 + i)
+    xo, xr = x.clone().to(DEV).requires_grad_(True), x.clone().requires_grad_(True)
+    yo, yr = ours(xo), ref(xr)
+    w = rand(tuple(yr.shape), 7100 + i)
+    (yo * w.to(DEV)).sum().backward()
+    (yr * w).sum().backward()
+    assert rel_l2(yo.detach().cpu(), yr.detach()) < 2e-4
+    assert rel_l2(xo.grad.cpu(), xr.grad) < 2e-4, name
+    for (n1, p1), (n2, p2) in zip(sorted(ours.named_parameters()), sorted(ref.named_parameters())):
+        assert n1 == n2 and p1.grad is not None
+        assert rel_l2(p1.grad.cpu(), p2.grad) < 2e-4, (name, n1)
+
+
+def test_dccrn_train_mode_step_vs_oracle():
+    """a full DCCRN-CL training-mode forward / backward through the module path (complex BN in batch-statistics
+    mode and the LSTM on stock PyTorch, every complex conv / STFT / mask / iSTFT through this package's nodes)."""
+    from speech_enhancement_b200 import training
+    args = ('dccrn-CL', 400, 100, 512)
+    ref = callers.DCCRN(*args, ops=OPS).train()
+    sd = seeded_state_dict(ref, seed=13)
+    ref.load_state_dict(sd)
+    ours = callers.DCCRN(*args).train()
+    ours.load_state_dict(sd)
+    ours.to(DEV)
+    mix, clean = synth_noisy_speech(2, 6000, seed=50), synth_noisy_speech(2, 6000, seed=51)
+    f_ref, f_ours = training.FlatGradients(ref), training.FlatGradients(ours)
+    with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        losses = []
+        for model, m, c in ((ref, mix, clean), (ours, mix.to(DEV), clean.to(DEV))):
+            _, wav = model(m)
+            loss = training.si_snr_loss(training.pad_or_truncate(wav, c), c)
+            loss.backward()
+            losses.append(loss.item())
+    assert abs(losses[0] - losses[1]) < 1e-3 * max(1.0, abs(losses[0]))
+    assert rel_l2(f_ours.buffer.cpu(), f_ref.buffer) < 5e-3
