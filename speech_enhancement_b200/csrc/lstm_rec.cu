@@ -12,6 +12,7 @@
 // words -- and h_{t-1} is broadcast from shared memory.  Two __syncthreads per step.
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/se_b200.h"
 
@@ -111,6 +112,147 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, 
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Cluster version (H = 128): the 512 gate columns of a row are split over a 2-CTA cluster -- CTA r owns
+// hidden units [64r, 64r+64) x 4 gates = 256 columns x 128 k = 32 K weights, ALL of them in registers
+// (512 threads x 64), so a step reads no weights from shared memory at all (the single-CTA kernel above
+// is bound by exactly that: 128 KB of shared-memory weight reads + the h broadcast per step).
+// Mapping: lane = k-slice of 4, warp = 16 columns; each thread does 16 x 4 FMAs on its own h slice (one
+// conflict-free LDS.128), then a 16-shuffle reduce-scatter leaves one column sum per lane pair.  The
+// new h halves are exchanged through distributed shared memory (st.shared::cluster into the peer's
+// double-buffered h) and ONE cluster barrier per step.
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void st_peer_f32(const float* local_ptr, uint32_t peer, float v) {
+  uint32_t la = static_cast<uint32_t>(__cvta_generic_to_shared(local_ptr)), ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(peer));
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
+}
+
+template <int R>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(512, 1)
+lstm_rec_cluster_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, const float* __restrict__ w_hh1,
+                        float* __restrict__ h_out0, float* __restrict__ h_out1, int64_t N, int64_t T, int64_t pre_ld) {
+  constexpr int H = 128, G = 512;
+  __shared__ __align__(16) float h_s[2][R][H];
+  __shared__ float g_s[R][256];
+  const float* __restrict__ w_hh = blockIdx.y ? w_hh1 : w_hh0;
+  float* __restrict__ h_out = blockIdx.y ? h_out1 : h_out0;
+  pre += blockIdx.y * G;
+  const uint32_t rank = cluster_rank(), peer = rank ^ 1u;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int gate = warp >> 2;                                    // warp-uniform
+  const int ubase = 64 * (int)rank + (warp & 3) * 16;            // first hidden unit of this warp's 16 columns
+  // weights of columns j(c) = gate*128 + ubase + c, k-slice [4*lane, 4*lane+4)
+  float w[16][4];
+#pragma unroll
+  for (int c = 0; c < 16; ++c) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(w_hh + (int64_t)(gate * H + ubase + c) * H + 4 * lane));
+    w[c][0] = v.x; w[c][1] = v.y; w[c][2] = v.z; w[c][3] = v.w;
+  }
+  // after the reduce-scatter lane l holds column c_l (lanes 2m, 2m+1 hold the same one)
+  const int c_l = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+  const int col_l = gate * H + ubase + c_l;                      // global gate column
+  const int slot_l = gate * 64 + (warp & 3) * 16 + c_l;          // g_s slot: [gate][unit within this CTA]
+  const bool loader = (lane & 1) == 0;
+  const int64_t nclusters = gridDim.x / 2, cid = blockIdx.x / 2;
+
+  for (int64_t row0 = cid * R; row0 < N; row0 += nclusters * R) {
+    const float* prow[R];
+    float nxt[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int64_t row = row0 + r < N ? row0 + r : N - 1;       // tail rows recompute the last row (never stored)
+      prow[r] = pre + row * T * pre_ld + col_l;
+      nxt[r] = loader ? __ldg(prow[r]) : 0.f;
+    }
+    float cst = 0.f;                                             // cell state of (row = tid/64, unit = tid%64)
+    for (int i = tid; i < R * H; i += 512) h_s[0][i / H][i % H] = 0.f;
+    cluster_barrier();
+    int cur = 0;
+    for (int64_t t = 0; t < T; ++t) {
+      float pg[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        pg[r] = nxt[r];
+        if (loader && t + 1 < T) nxt[r] = __ldg(prow[r] + (t + 1) * pre_ld);
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float4 hv = *reinterpret_cast<const float4*>(&h_s[cur][r][4 * lane]);
+        float p[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+          p[c] = fmaf(w[c][3], hv.w, fmaf(w[c][2], hv.z, fmaf(w[c][1], hv.y, w[c][0] * hv.x)));
+        // reduce-scatter over the 32 k-slices: 8 + 4 + 2 + 1 + 1 shuffles
+        {
+          const bool up = lane & 16;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float send = up ? p[c] : p[c + 8], keep = up ? p[c + 8] : p[c];
+            p[c] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+          }
+        }
+        {
+          const bool up = lane & 8;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float send = up ? p[c] : p[c + 4], keep = up ? p[c + 4] : p[c];
+            p[c] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+          }
+        }
+        {
+          const bool up = lane & 4;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const float send = up ? p[c] : p[c + 2], keep = up ? p[c + 2] : p[c];
+            p[c] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          }
+        }
+        {
+          const bool up = lane & 2;
+          const float send = up ? p[0] : p[1], keep = up ? p[1] : p[0];
+          p[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        }
+        p[0] += __shfl_xor_sync(0xffffffffu, p[0], 1);
+        if (loader) {
+          const float a = p[0] + pg[r];
+          g_s[r][slot_l] = gate == 2 ? tanhf_(a) : sigmoidf_(a);
+        }
+      }
+      __syncthreads();
+      if (tid < 64 * R) {
+        const int r = tid >> 6, u = tid & 63;
+        const float* g = g_s[r];
+        cst = g[64 + u] * cst + g[u] * g[128 + u];
+        const float h = g[192 + u] * tanhf_(cst);
+        float* dst = &h_s[cur ^ 1][r][64 * (int)rank + u];
+        *dst = h;
+        st_peer_f32(dst, peer, h);
+        if (row0 + r < N) h_out[((row0 + r) * T + t) * H + 64 * (int)rank + u] = h;
+      }
+      cluster_barrier();                                         // both h halves of step t are in place everywhere
+      cur ^= 1;
+    }
+  }
+}
+
+template <int R>
+static int launch_lstm_cluster(const float* pre, int64_t pre_ld, const float* w0, const float* w1, float* h0, float* h1,
+                               int nl, int64_t N, int64_t T, cudaStream_t s) {
+  int64_t clusters = (N + R - 1) / R;
+  const int64_t cap = num_sms() / 2 / nl;
+  if (clusters > cap) clusters = cap;
+  lstm_rec_cluster_kernel<R><<<dim3((unsigned)(2 * clusters), (unsigned)nl), 512, 0, s>>>(pre, w0, w1, h0, h1, N, T, pre_ld);
+  return check_launch("lstm_rec_cluster_kernel");
+}
+
 template <int H, int KR, int R>
 static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh0, const float* w_hh1, float* h_out0,
                        float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
@@ -143,7 +285,21 @@ static int dispatch_rows(const float* pre, int64_t pre_ld, const float* w0, cons
 
 static int lstm_rec_any(const float* pre, int64_t pre_ld, const float* w0, const float* w1, float* h0, float* h1, int nl,
                         int64_t N, int64_t T, int H, cudaStream_t s) {
-  if (H == 128) return dispatch_rows<128, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+  if (H == 128) {
+    static const char* single = getenv("SE_LSTM_SINGLE");      // tuning aid: keep the single-CTA kernel
+    if (single && atoi(single) != 0) return dispatch_rows<128, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+    // cluster kernel: 2 SMs per R rows; pick R so that the row jobs fit one wave of (#SMs / 2) clusters
+    // The cluster kernel (2 SMs per row, weights in registers) has the shorter step and wins while every row
+    // job gets its own cluster; at larger batches the step is issue-bound per row and the single-CTA kernel,
+    // which amortises its shared-memory weight reads over R rows, is ahead (measured: 64 x 4 s, 256 row jobs).
+    const int64_t slots = se::num_sms() / 2, jobs = N * nl;
+    static const char* force = getenv("SE_LSTM_CLUSTER");      // tuning aid: R of the cluster kernel to force
+    const int fr = force ? atoi(force) : 0;
+    if (fr == 4) return se::launch_lstm_cluster<4>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+    if (fr == 2) return se::launch_lstm_cluster<2>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+    if (fr == 1 || jobs <= slots) return se::launch_lstm_cluster<1>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+    return dispatch_rows<128, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+  }
   if (H == 64) return dispatch_rows<64, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
   return se::fail(SE_ERR_UNSUPPORTED, "se_lstm_rec_fwd: hidden size %d not supported (64 or 128)", H);
 }

@@ -545,3 +545,22 @@ def test_dccrn_train_mode_step_vs_oracle():
             losses.append(loss.item())
     assert abs(losses[0] - losses[1]) < 1e-3 * max(1.0, abs(losses[0]))
     assert rel_l2(f_ours.buffer.cpu(), f_ref.buffer) < 5e-3
+
+
+@pytest.mark.parametrize('cls,args,B,L', [(callers.DCCRN, ('dccrn-CL', 400, 100, 512), 2, 8000),
+                                          (callers.DCUNet, ('dcunet20', 512, 128, 512), 1, 16384)])
+def test_cuda_graph_replay_matches_eager(cls, args, B, L):
+    """the chained forward is capturable (no host sync, host-side tensor maps, cached operands): a CUDA-graph
+    replay returns exactly what the eager call returns, also after the input changes."""
+    from speech_enhancement_b200.graphs import GraphedInference
+    model = cls(*args).eval()
+    model.load_state_dict(seeded_state_dict(model, seed=14))
+    model.to(DEV)
+    g = GraphedInference(model)
+    for seed in (60, 61):
+        x = synth_noisy_speech(B, L, seed=seed).to(DEV)
+        with torch.no_grad():
+            spec_e, wav_e = model(x)
+        spec_g, wav_g = g(x)
+        assert torch.equal(wav_g, wav_e) and torch.equal(spec_g, spec_e)
+    assert len(g._graphs) == 1
