@@ -419,7 +419,7 @@ def run_ours(args):
         step(i)
     tot = st.totals_ms()
     st.close()
-    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm', 'linear'):
+    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm', 'linear', 'ccbam'):
         tot.setdefault(k, 0.0)
     win, hop, fft = MODEL['stft']
     T = (L + fft - win) // hop + 1
@@ -436,6 +436,7 @@ def run_ours(args):
     stages['cl2_convert_ms'] = tot['cl2'] / nprof
     stages['lstm_recurrence_ms'] = tot['lstm'] / nprof
     stages['lstm_linear_projections_ms'] = tot['linear'] / nprof
+    stages['ccbam_ms'] = tot['ccbam'] / nprof
     stages['step_ms'] = ms / args.steps
     stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / args.steps)
     roofline = {'bound': 'tensor', 'kernel': f'complex conv stack ({len(st.events.get("cconv", [])) // nprof} conv launches per step)',

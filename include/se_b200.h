@@ -190,6 +190,20 @@ SE_API int se_nc2_gather_w(const float* x, int64_t B, int C, int H, int W, int W
 SE_API int se_cconv_wgrad(const void* u_nc2, int Cu, int Hu, int Wu, const void* v_gather, int Cv, int Hv,
                           int64_t B, int kh, int kw, int sh, int ph, float* G, void* stream);
 
+/* ---- CCBAM attention on a CL2 skip activation (ccbam.py:28-106; SURVEY.md 8f side item) -----------------
+ * x_cl2 [B][2][P = H*W][Cp] bf16 hi|lo, C channels = [C/2 real | C/2 imaginary].
+ *   se_ccbam_channel_stats  partial [B][se_ccbam_num_partials(P)][2][Cp]: per-block sum and max over pixels
+ *                           (the caller finishes the tiny reduction: mean = sum(partials)/P, max = max(partials))
+ *   se_ccbam_spatial_pool   pooled [B][4][P] = mean, max over the real channels and mean, max over the
+ *                           imaginary channels of x * ca[b, c]                              (ccbam.py:71-80)
+ *   se_ccbam_apply          y_cl2 = x * ca[b, c] + sa[b, part(c)]  (sa [B][2][P])            (ccbam.py:98-106) */
+SE_API int se_ccbam_num_partials(int64_t P);
+SE_API int se_ccbam_channel_stats(const void* x_cl2, int64_t B, int64_t P, int C, int Cp, float* partial, void* stream);
+SE_API int se_ccbam_spatial_pool(const void* x_cl2, const float* ca, int64_t B, int64_t P, int C, int Cp, float* pooled,
+                                 void* stream);
+SE_API int se_ccbam_apply(const void* x_cl2, const float* ca, const float* sa, int64_t B, int64_t P, int C, int Cp,
+                          void* y_cl2, void* stream);
+
 /* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
  * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),
  * so slices of the STFT output and of the decoder output are consumed in place.  For

@@ -52,6 +52,10 @@ _SIGS = {
     'se_nc2_gather_elems': (C.c_int64, [_L, _I, _I, _I, _I]),
     'se_nc2_gather_w': (C.c_int, [_P, _L, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     'se_cconv_wgrad': (C.c_int, [_P, _I, _I, _I, _P, _I, _I, _L, _I, _I, _I, _I, _P, _P]),
+    'se_ccbam_num_partials': (C.c_int, [_L]),
+    'se_ccbam_channel_stats': (C.c_int, [_P, _L, _L, _I, _I, _P, _P]),
+    'se_ccbam_spatial_pool': (C.c_int, [_P, _P, _L, _L, _I, _I, _P, _P]),
+    'se_ccbam_apply': (C.c_int, [_P, _P, _P, _L, _L, _I, _I, _P, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_mask_bwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P, _P, _P, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),

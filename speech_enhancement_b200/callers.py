@@ -369,6 +369,32 @@ class CCBAM(nn.Module):
         self.channel_attention_branch = _ChannelAttention(feature_map_channels, reduction)
         self.spatial_attention_branch = _SpatialAttention(ops)
 
+    def forward_cl2(self, act):
+        """the same attention on a CL2 activation (chain.Act) in three passes of csrc/ccbam.cu; the shared
+        MLP, the 7x7 attention convolution and the sigmoids run on their tiny tensors as usual."""
+        from . import _abi
+        from .chain import Act
+        x = act.data
+        B, _, H, W, Cp = x.shape
+        if (H, W) != (act.H, act.W):
+            raise RuntimeError('CCBAM.forward_cl2: trimmed activations are not supported')
+        C, P = act.C, H * W
+        lib = _abi.lib()
+        with torch.cuda.device(x.device), _abi.stage('ccbam'):
+            nb = lib.se_ccbam_num_partials(P)
+            partial = torch.empty((B, nb, 2, Cp), device=x.device, dtype=torch.float32)
+            _abi.check(lib.se_ccbam_channel_stats(_abi.ptr(x), B, P, C, Cp, _abi.ptr(partial), _abi.stream_ptr()))
+            fc = self.channel_attention_branch.shared_fc_layer
+            ca = torch.sigmoid(fc(partial[:, :, 0, :C].sum(1) / P) + fc(partial[:, :, 1, :C].amax(1))).contiguous()
+            pooled = torch.empty((B, 4, H, W), device=x.device, dtype=torch.float32)
+            _abi.check(lib.se_ccbam_spatial_pool(_abi.ptr(x), _abi.ptr(ca), B, P, C, Cp, _abi.ptr(pooled),
+                                                 _abi.stream_ptr()))
+            sa = torch.sigmoid(self.spatial_attention_branch.conv(pooled)).contiguous()
+            out = torch.empty_like(x)
+            _abi.check(lib.se_ccbam_apply(_abi.ptr(x), _abi.ptr(ca), _abi.ptr(sa), B, P, C, Cp, _abi.ptr(out),
+                                          _abi.stream_ptr()))
+        return Act(out, C, H, W)
+
     def forward(self, x):
         x = x * self.channel_attention_branch(x)
         sa = self.spatial_attention_branch(x)
@@ -423,27 +449,26 @@ class FRCRN(nn.Module):
 
     def _forward_fused(self, x):
         """encoder / decoder convolutions chained in CL2 (BN + LeakyReLU folded, causal pad as a coordinate
-        shift, complex_concat as a second source, the bottom-row F.pad by out-of-bounds fill); the CCBAM
-        attention on the skips, the LSTM and the real final_conv keep their own paths."""
+        shift, complex_concat as a second source, the bottom-row F.pad by out-of-bounds fill), the CCBAM
+        attention applied to the CL2 skips by csrc/ccbam.cu; the real final_conv stays on cuDNN."""
         from .chain import cl2_from_nchw
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)
         B, C2, T = spec.shape
         noisy_real, noisy_imag = _spec_planes(spec, n_bins)
         enc, dec = self._fused_blocks()
-        act, nchw = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1,
-                                       out_nchw=True)
-        skips = [nchw]
+        act, nchw = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1)
+        skips = [act]
         for i in range(1, len(enc)):
-            act, nchw = enc[i]([act], pad_left=1, out_cl2=True, out_nchw=True)
-            skips.append(nchw)
+            act, nchw = enc[i]([act], pad_left=1, out_cl2=True, out_nchw=i == len(enc) - 1)
+            skips.append(act)
         b, c, f, t = nchw.shape
         h = self.lstm(nchw.reshape(b, c * f, t).permute(0, 2, 1))
         act = cl2_from_nchw(h.permute(0, 2, 1).reshape(b, c, f, t))
         y = None
         n = len(dec)
         for i, (att, blk) in enumerate(zip(self.decoder.skip_connection_attention_layers, dec)):
-            skip = cl2_from_nchw(att(skips.pop()))
+            skip = att.forward_cl2(skips.pop())
             if act.W > skip.W:
                 act = act.trimmed(W=skip.W)
             act, y = blk([act, skip], out_cl2=i < n - 1, out_nchw=i == n - 1)
