@@ -434,6 +434,7 @@ class FRCRN(nn.Module):
 
     fused = True
     _fb = None
+    _final_fb = None
 
     def _fused_blocks(self):
         if self._fb is None:
@@ -447,10 +448,17 @@ class FRCRN(nn.Module):
             self._fb = (enc, dec)
         return self._fb
 
+    def _final_block(self):
+        if self._final_fb is None:
+            from .chain import RealConvBlock
+            self._final_fb = RealConvBlock(self.final_conv)
+        return self._final_fb
+
     def _forward_fused(self, x):
         """encoder / decoder convolutions chained in CL2 (BN + LeakyReLU folded, causal pad as a coordinate
         shift, complex_concat as a second source, the bottom-row F.pad by out-of-bounds fill), the CCBAM
-        attention applied to the CL2 skips by csrc/ccbam.cu; the real final_conv stays on cuDNN."""
+        attention applied to the CL2 skips by csrc/ccbam.cu; the real final_conv reads the last decoder's CL2
+        output as a RealConvBlock."""
         from .chain import cl2_from_nchw
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)
@@ -471,9 +479,8 @@ class FRCRN(nn.Module):
             skip = att.forward_cl2(skips.pop())
             if act.W > skip.W:
                 act = act.trimmed(W=skip.W)
-            act, y = blk([act, skip], out_cl2=i < n - 1, out_nchw=i == n - 1)
-        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
-            y = self.final_conv(y)                                        # [B, 2, F-2, T]
+            act, _ = blk([act, skip], out_cl2=True, out_nchw=False)
+        _, y = self._final_block()([act], out_cl2=False, out_nchw=True)   # [B, 2, F-2, T]
         est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, y[:, 0], y[:, 1])
         wav = self.istft(est_spec)
         return est_spec, torch.clamp_(wav, -1, 1)

@@ -146,9 +146,7 @@ class FusedBlock:
     def _operands(self):
         conv, norm = self.conv, self.norm
         slope_const, slope_t = _slope_of(self.act)
-        ts = [conv.real_conv.weight, conv.imag_conv.weight]
-        if conv.real_conv.bias is not None:
-            ts += [conv.real_conv.bias, conv.imag_conv.bias]
+        ts = self._param_tensors()
         has_bn = norm is not None and not isinstance(norm, nn.Identity)
         if has_bn:
             if norm.training or not norm.track_running_stats:
@@ -161,7 +159,7 @@ class FusedBlock:
         if key == self._key:
             return self._ops
         with torch.no_grad():
-            packed, bias, co, ci, kh, kw = conv._packed()           # fp32 [2co, 2ci*kh*kw], [2co] | None
+            packed, bias, co, ci, kh, kw = self._packed_source()    # fp32 [2co, 2ci*kh*kw], [2co] | None
             dev = packed.device
             if bias is None:
                 bias = torch.zeros(2 * co, device=dev, dtype=torch.float32)
@@ -197,6 +195,16 @@ class FusedBlock:
         self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt, 'wq_sc': wq_sc}
         self._key = key
         return self._ops
+
+    def _param_tensors(self):
+        conv = self.conv
+        ts = [conv.real_conv.weight, conv.imag_conv.weight]
+        if conv.real_conv.bias is not None:
+            ts += [conv.real_conv.bias, conv.imag_conv.bias]
+        return ts
+
+    def _packed_source(self):
+        return self.conv._packed()
 
     def out_size(self, H, W, pad_top=0, pad_left=0):
         if self.transposed:
@@ -267,6 +275,36 @@ class FusedBlock:
                 self.pw, _abi.ptr(y), _abi.ptr(y_act.data) if y_act is not None else None,
                 y_act.Cp if y_act is not None else 0, Ho, Wo, _abi.stream_ptr()))
         return y_act, y
+
+
+class RealConvBlock(FusedBlock):
+    """a plain (real) nn.Conv2d with even channel counts on the chained engine: its weight is already the
+    packed operand [Cout, Cin*kh*kw] (FRCRN's final_conv, /root/reference/models/frcrn.py:final_conv)."""
+
+    def __init__(self, conv, act=None):
+        w = conv.weight
+        if w.shape[0] % 2 or w.shape[1] % 2 or _pair(conv.dilation) != (1, 1) or conv.groups != 1:
+            raise RuntimeError('RealConvBlock: needs even channel counts, no dilation, groups == 1')
+        self.conv, self.norm, self.act = conv, None, act
+        self.transposed = False
+        self.cout2, self.cin2 = w.shape[0], w.shape[1]
+        self.kh, self.kw = w.shape[2], w.shape[3]
+        self.sh, self.sw = _pair(conv.stride)
+        self.ph, self.pw = _pair(conv.padding)
+        self.oph, self.opw = 0, 0
+        self.src_channels = [self.cin2]
+        self.concat = 'plain'
+        self.scatter_form = False
+        self._key = None
+        self._ops = None
+
+    def _param_tensors(self):
+        return [self.conv.weight] + ([self.conv.bias] if self.conv.bias is not None else [])
+
+    def _packed_source(self):
+        w = self.conv.weight.detach().float()
+        b = self.conv.bias.detach().float() if self.conv.bias is not None else None
+        return w.reshape(w.shape[0], -1), b, w.shape[0] // 2, w.shape[1] // 2, w.shape[2], w.shape[3]
 
 
 class LinearOperand:

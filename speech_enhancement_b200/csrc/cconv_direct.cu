@@ -20,11 +20,15 @@ struct SmallCinParams {
 
 constexpr int kSmallCinMaxK = 512;
 
+// CW = output channels held in registers per pass: 32 for the encoder layers (and any CL2 store),
+// 4 / 8 for the few-channel convs (the CCBAM 7x7 spatial-attention conv has Cout2 = 2), where a
+// 32-wide pass would spend 16x the FMAs on zero weights.
+template <int CW>
 __global__ void __launch_bounds__(128)
 cconv_small_cin_kernel(const SmallCinParams p) {
-  extern __shared__ float w_s[];                  // [K][Cout2r]  (Cout2 rounded up to 32)
+  extern __shared__ float w_s[];                  // [K][Cout2r]  (Cout2 rounded up to CW)
   const int K = p.Cin2 * p.kh * p.kw;
-  const int Cr = (p.Cout2 + 31) / 32 * 32;
+  const int Cr = (p.Cout2 + CW - 1) / CW * CW;
   for (int i = threadIdx.x; i < K * Cr; i += blockDim.x) {
     int k = i / Cr, co = i - k * Cr;
     w_s[i] = co < p.Cout2 ? __ldg(p.w + (int64_t)co * K + k) : 0.f;
@@ -37,10 +41,10 @@ cconv_small_cin_kernel(const SmallCinParams p) {
   const int64_t plane = (int64_t)p.Ho * p.Wo;
   const int64_t pix = (int64_t)ho * p.Wo + wo;
   const int cmax = p.y_cl2 != nullptr && p.y_Cp > Cr ? p.y_Cp : Cr;
-  for (int c0 = 0; c0 < cmax; c0 += 32) {
-    float acc[32];
+  for (int c0 = 0; c0 < cmax; c0 += CW) {
+    float acc[CW];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+    for (int j = 0; j < CW; ++j) acc[j] = 0.f;
     if (c0 < Cr) {
       // walk the K = Cin2*kh*kw taps; inputs come from L1 after the first pass (zero padding + the
       // caller's causal pad are the bounds checks)
@@ -55,7 +59,7 @@ cconv_small_cin_kernel(const SmallCinParams p) {
             const float xk = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + w) : 0.f;
             const float4* wr = reinterpret_cast<const float4*>(w_s + k * Cr + c0);
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
+            for (int j4 = 0; j4 < CW / 4; ++j4) {
               const float4 w4 = wr[j4];
               acc[4 * j4 + 0] = fmaf(w4.x, xk, acc[4 * j4 + 0]);
               acc[4 * j4 + 1] = fmaf(w4.y, xk, acc[4 * j4 + 1]);
@@ -66,7 +70,7 @@ cconv_small_cin_kernel(const SmallCinParams p) {
         }
     }
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
+    for (int j = 0; j < CW; ++j) {
       const int co = c0 + j;
       float f = acc[j];
       if (co < p.Cout2 && p.bias != nullptr) f += __ldg(p.bias + co);
@@ -74,10 +78,10 @@ cconv_small_cin_kernel(const SmallCinParams p) {
     }
     if (p.y != nullptr) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < CW; ++j)
         if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc[j];
     }
-    if (p.y_cl2 != nullptr && c0 < p.y_Cp) {
+    if constexpr (CW == 32) if (p.y_cl2 != nullptr && c0 < p.y_Cp) {
       __align__(16) __nv_bfloat16 hi[32];
       __align__(16) __nv_bfloat16 lo[32];
 #pragma unroll
@@ -109,7 +113,8 @@ extern "C" int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, in
   SE_REQUIRE(Ho == (H + pad_top + 2 * ph - kh) / sh + 1 && Wo == (W + pad_left + 2 * pw - kw) / sw + 1,
              "se_cconv_small_cin: output size does not match geometry");
   SE_REQUIRE(y_cl2 == nullptr || (y_Cp >= Cout2 && y_Cp % 64 == 0), "se_cconv_small_cin: bad y_Cp");
-  const int K = Cin2 * kh * kw, Cr = (Cout2 + 31) / 32 * 32;
+  const int CW = (y_cl2 != nullptr || Cout2 > 8) ? 32 : (Cout2 > 4 ? 8 : 4);
+  const int K = Cin2 * kh * kw, Cr = (Cout2 + CW - 1) / CW * CW;
   if (K > se::kSmallCinMaxK || (size_t)K * Cr * 4 > 160 * 1024)
     return se::fail(SE_ERR_UNSUPPORTED, "se_cconv_small_cin: needs Cin2*kh*kw <= %d", se::kSmallCinMaxK);
   if (B == 0) return SE_OK;
@@ -118,12 +123,14 @@ extern "C" int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, in
                        packed, bias, slope, y_nchw, reinterpret_cast<__nv_bfloat16*>(y_cl2), y_Cp};
   const int smem = K * Cr * 4;
   static int smem_attr = 48 * 1024;
-  if (smem > smem_attr) {
-    SE_CUDA(cudaFuncSetAttribute(se::cconv_small_cin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  if (smem > smem_attr) {                         // only the 32-wide pass can exceed the default
+    SE_CUDA(cudaFuncSetAttribute(se::cconv_small_cin_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     smem_attr = smem;
   }
   dim3 grid((unsigned)((Wo + 127) / 128), (unsigned)Ho, (unsigned)B);
-  se::cconv_small_cin_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(p);
+  if (CW == 32) se::cconv_small_cin_kernel<32><<<grid, 128, smem, (cudaStream_t)stream>>>(p);
+  else if (CW == 8) se::cconv_small_cin_kernel<8><<<grid, 128, smem, (cudaStream_t)stream>>>(p);
+  else se::cconv_small_cin_kernel<4><<<grid, 128, smem, (cudaStream_t)stream>>>(p);
   return se::check_launch("se_cconv_small_cin");
 }
 
