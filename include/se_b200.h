@@ -76,6 +76,25 @@ SE_API int se_istft_fwd(const float* spec, const float* phase_or_null, const flo
                  const float* window, int64_t B, int C2, int64_t T, int win, int hop,
                  int64_t crop_front, int64_t out_len, float* out, void* stream);
 
+/* ---- FFT engine for ConvSTFT / ConviSTFT (HBM-bound; csrc/stft_fft.cu) --------------------------------
+ * Valid when the module's basis IS the windowed real DFT of conv_stft.py:7-26 (`weight[c, 0, n]` =
+ * window[n] * cos / -sin(2 pi f n / fft), inverse: window[n] * pinv(.)^T) -- the host shim verifies the
+ * buffer against that closed form and otherwise stays on the dense engines above, so a checkpoint with a
+ * different basis is still honoured.  window [win] is row 0 of the forward `weight` (forward) / the
+ * module's `window` buffer (inverse).
+ *   se_stft_fft_fwd    x [B, L] -> out [B, fft+2, T]: reflect pad (pad = 0 when center is False), window,
+ *                      512-point real FFT per frame                                   (conv_stft.py:48-56)
+ *   se_istft_fft_fwd   spec [B, fft+2, T] -> out [B, out_len]: inverse FFT + the rank-2 pseudo-inverse
+ *                      term, window, overlap-add, * scale[n] (= 1 / (sum window^2 + 1e-8), [(T+J-1)*hop],
+ *                      NULL = 1), crop [crop_front, crop_front + out_len)            (conv_stft.py:101-114)
+ *   se_stft_fft_supported  1 when (win, hop, fft) is covered: fft == 512, win <= fft, hop <= 256,
+ *                      ceil(win / hop) <= 8                                                              */
+SE_API int se_stft_fft_supported(int win, int hop, int fft);
+SE_API int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
+                           int pad, float* out, int64_t T, void* stream);
+SE_API int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
+                            const float* scale, int64_t crop_front, int64_t out_len, float* out, void* stream);
+
 /* ---- ComplexConv2d / ComplexConvTranspose2d (complex_nn.py:52-91) ----------------------------
  * se_cconv_pack_weight: Wr, Wi are the real_conv / imag_conv weights
  *   (conv: [Co, Ci, kh, kw]; transposed: [Ci, Co, kh, kw]); packed is the real GEMM operand

@@ -37,7 +37,7 @@ def main():
     a = ap.parse_args()
     dev = 'cuda:0'
     x = torch.randn(a.batch, a.len, device=dev) * 0.1
-    for engine in ('simt', 'umma'):
+    for engine in ('simt', 'umma', 'fft'):
         st = se.ConvSTFT(a.win, a.hop, a.fft).to(dev)
         ist = se.ConviSTFT(a.win, a.hop, a.fft).to(dev)
         st.engine = ist.engine = engine

@@ -38,7 +38,7 @@ def timeit(fn, iters, flush):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--engine', default='auto', choices=['auto', 'simt', 'umma'])
+    ap.add_argument('--engine', default='auto', choices=['auto', 'simt', 'umma', 'fft'])
     ap.add_argument('--iters', type=int, default=5)
     ap.add_argument('--cap', type=int, default=1 << 26, help='max B*L samples per point')
     a = ap.parse_args()

@@ -59,6 +59,9 @@ _SIGS = {
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_mask_bwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P, _P, _P, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),
+    'se_stft_fft_supported': (C.c_int, [_I, _I, _I]),
+    'se_stft_fft_fwd': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _I, _P, _L, _P]),
+    'se_istft_fft_fwd': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _P, _L, _L, _P, _P]),
 }
 
 

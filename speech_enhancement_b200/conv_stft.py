@@ -15,8 +15,11 @@ import torch.nn.functional as F
 from . import _abi
 
 # engine selection (class attribute `engine` on both modules):
-#   'auto'  tensor cores whenever the framing fits the conv engine, else the SIMT kernels
-#   'umma'  tensor cores or raise;  'simt' the exact-fp32 SIMT kernels (stft_simt.cu)
+#   'auto'  the FFT kernels (stft_fft.cu) when `weight` is the windowed real-DFT basis of init_kernels and the
+#           framing is covered (fft 512); else tensor cores when the framing fits the conv engine; else SIMT
+#   'fft'   FFT kernels or raise;  'umma'  tensor cores or raise;  'simt' the exact-fp32 SIMT kernels
+#   (stft_simt.cu).  Every engine consumes the module's own buffers: a checkpoint whose basis is NOT the closed
+#   form fails the check below and is projected densely.
 _MAX_TAPS = 16          # ceil(win / hop) taps per launch (se_cconv_gemm allows 49 in total)
 
 
@@ -54,6 +57,32 @@ def init_kernels(window_size, fft_size, win_type='hann', inverse=False):
     kernel = (kernel * window)[:, None, :]
     return (torch.from_numpy(kernel.astype(np.float32)),
             torch.from_numpy(window[None, :, None].astype(np.float32)))
+
+
+def _dft_rows(win, fft, device):
+    """[cos; -sin](2 pi f n / fft), f = 0..fft/2, n = 0..win-1, float64 [fft+2, win] (conv_stft.py:11-15)"""
+    n = torch.arange(win, device=device, dtype=torch.int64)[None, :]
+    f = torch.arange(fft // 2 + 1, device=device, dtype=torch.int64)[:, None]
+    phase = (2.0 * np.pi / fft) * ((f * n) % fft).double()
+    return torch.cat([torch.cos(phase), -torch.sin(phase)], 0)
+
+
+def _is_dft_basis(weight, window, fft, inverse):
+    """True when `weight` [fft+2, 1, win] equals the closed form the FFT kernels implement, to fp32 rounding:
+    forward  window[n] * [cos; -sin](2 pi f n / fft);  inverse  window[n] * pinv(K)^T with
+    pinv(K)^T = K (K^T K)^-1 and K^T K = (fft/2) I + e e^T + o o^T (e / o = even / odd sample indicators)."""
+    c2, _, win = weight.shape
+    if c2 != fft + 2 or win > fft or window.numel() != win:
+        return False
+    w = weight.detach()[:, 0, :].double()
+    K = _dft_rows(win, fft, weight.device)
+    if inverse:
+        a = fft / 2.0
+        par = (torch.arange(win, device=weight.device) % 2).double()
+        e, o = 1.0 - par, par
+        K = (K - torch.outer(K @ e, e) / (a + e.sum()) - torch.outer(K @ o, o) / (a + o.sum())) / a
+    ref = K * window.detach().reshape(1, win).double()
+    return bool(((w - ref).abs().max() <= 2e-6 * ref.abs().max()).item())
 
 
 def _no_grad_only(name, *tensors):
@@ -171,6 +200,31 @@ class ConvSTFT(nn.Module):
 
     engine = 'auto'
 
+    def _fft_ready(self, window, inverse):
+        """the FFT kernels apply: framing covered and `weight` is the closed-form basis (checked once per
+        weight version, on the device)"""
+        w = self.weight
+        key = (w.data_ptr(), w._version, window.data_ptr(), window._version, w.device)
+        c = self.__dict__.get('_fft_check')
+        if c is None or c[0] != key:
+            ok = (_abi.lib().se_stft_fft_supported(self.window_size, self.hop_size, self.fft_size) == 1
+                  and _is_dft_basis(w, window, self.fft_size, inverse))
+            c = self.__dict__['_fft_check'] = (key, ok)
+        return c[1]
+
+    def _pick_engine(self, name, window, inverse, nonempty=True):
+        win, hop = self.window_size, self.hop_size
+        if self.engine in ('auto', 'fft') and nonempty and self._fft_ready(window, inverse):
+            return 'fft'
+        if self.engine == 'fft':
+            raise RuntimeError(f'{name}: window {win} / hop {hop} / fft {self.fft_size} (or a `weight` that is not the '
+                               'windowed DFT basis) is outside the FFT engine')
+        if self.engine != 'simt' and _tc_ok(win, hop) and nonempty:
+            return 'umma'
+        if self.engine == 'umma':
+            raise RuntimeError(f'{name}: window {win} / hop {hop} does not fit the tensor-core framing')
+        return 'simt'
+
     def _cached(self, slot, build):
         w = self.weight
         key = (slot, w.data_ptr(), w._version, w.device)
@@ -188,11 +242,13 @@ class ConvSTFT(nn.Module):
         pad = self.pad if self.center else 0
         T = (L + 2 * pad - win) // self.hop_size + 1
         out = torch.empty((B, c2, T), device=x.device, dtype=torch.float32)
-        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size) and B > 0
-        if self.engine == 'umma' and not tc:
-            raise RuntimeError(f'ConvSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
+        window = w[0, 0]                                  # row f = 0 of the real block is the analysis window
+        eng = self._pick_engine('ConvSTFT', window, False, B > 0)
         with torch.cuda.device(x.device), _abi.stage('stft'):
-            if tc:
+            if eng == 'fft':
+                _abi.check(_abi.lib().se_stft_fft_fwd(_abi.ptr(x), B, L, _abi.ptr(window), win, self.hop_size,
+                                                      self.fft_size, pad, _abi.ptr(out), T, _abi.stream_ptr()))
+            elif eng == 'umma':
                 _frames_project(x, self._cached('fwd', _frames_operand), self.hop_size, pad, T, out)
             else:
                 _abi.check(_abi.lib().se_stft_fwd(_abi.ptr(x), B, L, _abi.ptr(w.contiguous()), c2, win, self.hop_size,
@@ -281,6 +337,8 @@ class ConviSTFT(nn.Module):
     engine = 'auto'
 
     _cached = ConvSTFT._cached
+    _fft_ready = ConvSTFT._fft_ready
+    _pick_engine = ConvSTFT._pick_engine
 
     def _ola_scale(self, T, J):
         """1 / (sum of squared windows + 1e-8) per output sample (conv_stft.py:101-106), [Q*hop]."""
@@ -303,11 +361,14 @@ class ConviSTFT(nn.Module):
         c2, _, win = w.shape
         B, _, T = spec.shape
         out = torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
-        tc = self.engine != 'simt' and _tc_ok(win, self.hop_size)
-        if self.engine == 'umma' and not tc:
-            raise RuntimeError(f'ConviSTFT: window {win} / hop {self.hop_size} does not fit the tensor-core framing')
+        eng = self._pick_engine('ConviSTFT', self.window, True)
         with torch.cuda.device(spec.device), _abi.stage('istft'):
-            if tc:
+            if eng == 'fft':
+                J = -(-win // self.hop_size)
+                _abi.check(_abi.lib().se_istft_fft_fwd(_abi.ptr(spec), B, T, _abi.ptr(self.window), win, self.hop_size,
+                                                       self.fft_size, _abi.ptr(self._ola_scale(T, J)), start, out_len,
+                                                       _abi.ptr(out), _abi.stream_ptr()))
+            elif eng == 'umma':
                 operand = self._cached('fwd', _ola_operand)
                 _overlap_add(spec, operand, self.hop_size, self._ola_scale(T, operand[0]), out, start, out_len)
             else:

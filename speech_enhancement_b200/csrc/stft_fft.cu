@@ -1,0 +1,485 @@
+// ConvSTFT / ConviSTFT as shared-memory FFTs: the HBM-bound engine of the STFT front / back end.
+//
+// The reference projects every frame onto a dense windowed real-DFT basis with F.conv1d
+// (/root/reference/models/conv_stft.py:56) and inverts with F.conv_transpose1d against pinv(basis) * window
+// (:17-20, :101).  When the module's `weight` buffer IS that basis (the host checks it against the closed form
+// before choosing this engine) the projection is  window -> 512-point real FFT  and the inverse is
+//   y_t[m] = window[m]/N * ( z_t[m] - S_parity(m) / (N/2 + n_parity(m)) ),   z_t[m] = 2 Re sum'_f X_t[f] e^{+2 pi i f m / N}
+// (sum' counts DC and Nyquist once without their imaginary parts; S_even / S_odd are the sums of z_t over the even /
+// odd samples below `win`, n_even / n_odd how many there are) -- the rank-2 term is what pinv of the TRUNCATED DFT
+// adds to a plain inverse FFT:  K^T K = (N/2) I + e e^T + o o^T  for the first `win` rows of rfft(eye(N)).
+// ~25x fewer FLOPs than the dense projection, all in exact fp32 on the CUDA cores, so both directions move
+// their algorithmic bytes once: wave -> spectrum (4(L + C2 T) B/utt) and spectrum -> wave.
+//
+// Work decomposition (both kernels): one CTA per (utterance, tile of <= 32 frames / hop blocks), 8 warps.
+// A warp transforms TWO frames at a time as one 512-point complex FFT (frame A real part, frame B imaginary
+// part): 16 points per lane, radix-16 in registers, one transpose through shared memory, radix-16 in registers
+// again and a final radix-2 across lane pairs (shfl.xor 16).  Spectra / frames of the whole tile are staged in
+// shared memory so that every global access is a contiguous run along the frame axis.
+#include <utility>
+#include "common.cuh"
+
+namespace se {
+namespace {
+
+constexpr int NFFT = 512;       // points of the complex FFT (= fft_size)
+constexpr int TILE = 32;        // frames (forward) / hop blocks (inverse) per CTA
+constexpr int THREADS = 256;
+constexpr int WARPS = THREADS / 32;
+constexpr int ZPITCH = 529;     // float2 per pair row: >= 16*33 transpose scratch, odd -> conflict-free columns
+constexpr int TPITCH = 33;      // transpose scratch row pitch (float2)
+constexpr int MAXJ = 8;         // ceil(win / hop) covered by the inverse kernel
+
+template <int... I, class F>
+__device__ __forceinline__ void static_for_impl(std::integer_sequence<int, I...>, F&& f) {
+  (f(std::integral_constant<int, I>{}), ...);
+}
+template <int N, class F>
+__device__ __forceinline__ void static_for(F&& f) { static_for_impl(std::make_integer_sequence<int, N>{}, f); }
+
+__host__ __device__ constexpr int brev4(int k) { return ((k & 1) << 3) | ((k & 2) << 1) | ((k & 4) >> 1) | ((k & 8) >> 3); }
+
+// cos / sin of 2 pi j / 32, j = 0..15
+__host__ __device__ constexpr float cos32(int j) {
+  constexpr float t[16] = {1.0f, 0.98078528040323043f, 0.92387953251128674f, 0.83146961230254524f,
+                           0.70710678118654752f, 0.55557023301960218f, 0.38268343236508978f, 0.19509032201612825f,
+                           0.0f, -0.19509032201612825f, -0.38268343236508978f, -0.55557023301960218f,
+                           -0.70710678118654752f, -0.83146961230254524f, -0.92387953251128674f, -0.98078528040323043f};
+  return t[j];
+}
+__host__ __device__ constexpr float sin32(int j) {
+  constexpr float t[16] = {0.0f, 0.19509032201612825f, 0.38268343236508978f, 0.55557023301960218f,
+                           0.70710678118654752f, 0.83146961230254524f, 0.92387953251128674f, 0.98078528040323043f,
+                           1.0f, 0.98078528040323043f, 0.92387953251128674f, 0.83146961230254524f,
+                           0.70710678118654752f, 0.55557023301960218f, 0.38268343236508978f, 0.19509032201612825f};
+  return t[j];
+}
+
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// a * (c - i s) forward, a * (c + i s) inverse
+template <bool INV>
+__device__ __forceinline__ float2 cmul_w(float2 a, float c, float s) {
+  if (INV) return make_float2(fmaf(a.x, c, -a.y * s), fmaf(a.y, c, a.x * s));
+  return make_float2(fmaf(a.x, c, a.y * s), fmaf(a.y, c, -a.x * s));
+}
+// a * W16^J (forward: exp(-2 pi i J / 16), inverse: conjugate), J in [0, 8)
+template <int J, bool INV>
+__device__ __forceinline__ float2 twid16(float2 a) {
+  if constexpr (J == 0) return a;
+  else if constexpr (J == 4) return INV ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
+  else return cmul_w<INV>(a, cos32(2 * J), sin32(2 * J));
+}
+
+// 16-point DFT in registers, radix-2 decimation in frequency; X[k] ends up in v[brev4(k)]
+template <bool INV>
+__device__ __forceinline__ void fft16(float2 (&v)[16]) {
+  static_for<8>([&](auto j_) {
+    constexpr int j = decltype(j_)::value;
+    float2 u = v[j], w = v[j + 8];
+    v[j] = cadd(u, w);
+    v[j + 8] = twid16<j, INV>(csub(u, w));
+  });
+  static_for<8>([&](auto i_) {
+    constexpr int j = decltype(i_)::value & 3, i = (decltype(i_)::value >> 2) * 8 + j;
+    float2 u = v[i], w = v[i + 4];
+    v[i] = cadd(u, w);
+    v[i + 4] = twid16<2 * j, INV>(csub(u, w));
+  });
+  static_for<8>([&](auto i_) {
+    constexpr int j = decltype(i_)::value & 1, i = (decltype(i_)::value >> 1) * 4 + j;
+    float2 u = v[i], w = v[i + 2];
+    v[i] = cadd(u, w);
+    v[i + 2] = twid16<4 * j, INV>(csub(u, w));
+  });
+  static_for<8>([&](auto i_) {
+    constexpr int i = decltype(i_)::value * 2;
+    float2 u = v[i], w = v[i + 1];
+    v[i] = cadd(u, w);
+    v[i + 1] = csub(u, w);
+  });
+}
+
+// 512-point complex DFT of one warp: on entry lane n1 holds z[n1 + 32 n2] in v[n2]; on exit lane (h = lane >> 4,
+// k2 = lane & 15) holds Z[16 k + 256 h + k2] in v[k].  tw[k2] = exp(-+2 pi i lane k2 / 512) (cos, sin magnitudes).
+// `row` is this pair's scratch row (>= 16 * TPITCH float2); the caller owns it exclusively.
+template <bool INV>
+__device__ __forceinline__ void warp_fft512(float2 (&v)[16], const float2 (&tw)[16], float2* row, int lane) {
+  fft16<INV>(v);
+  static_for<16>([&](auto k2_) {
+    constexpr int k2 = decltype(k2_)::value;
+    float2 y = v[brev4(k2)];
+    if constexpr (k2 != 0) y = cmul_w<INV>(y, tw[k2].x, tw[k2].y);
+    row[k2 * TPITCH + lane] = y;
+  });
+  __syncwarp();
+  const int h = lane >> 4, k2l = lane & 15;
+  static_for<16>([&](auto m_) {
+    constexpr int m = decltype(m_)::value; v[m] = row[k2l * TPITCH + 2 * m + h]; });
+  __syncwarp();
+  fft16<INV>(v);
+  float2 r[16];
+  const float sgn = h ? -1.0f : 1.0f;
+  static_for<16>([&](auto k_) {
+    constexpr int k = decltype(k_)::value;
+    float2 mine = v[brev4(k)];
+    // odd half: times W32^k before the last butterfly
+    if constexpr (k != 0) {
+      float c = h ? cos32(k) : 1.0f, s = h ? sin32(k) : 0.0f;
+      mine = cmul_w<INV>(mine, c, s);
+    }
+    float2 other = make_float2(__shfl_xor_sync(0xffffffffu, mine.x, 16), __shfl_xor_sync(0xffffffffu, mine.y, 16));
+    r[k] = make_float2(fmaf(sgn, mine.x, other.x), fmaf(sgn, mine.y, other.y));   // E + O' (h = 0) / E - O' (h = 1)
+  });
+  static_for<16>([&](auto k_) {
+    constexpr int k = decltype(k_)::value; v[k] = r[k]; });
+}
+
+__device__ __forceinline__ void lane_twiddles(float2 (&tw)[16], int lane) {
+  static_for<16>([&](auto k2_) {
+    constexpr int k2 = decltype(k2_)::value;
+    float s, c;
+    sincospif((float)(lane * k2) * (1.0f / 256.0f), &s, &c);     // angle 2 pi lane k2 / 512
+    tw[k2] = make_float2(c, s);
+  });
+}
+
+// 4-byte asynchronous global -> shared copy (LDGSTS): the staging loops issue all of a tile's copies back to back
+// and wait once, so the memory system sees the whole tile in flight.  `valid == false` writes 0.
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid = true) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  int sz = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async8(float* smem_dst, const float* gsrc, bool valid = true) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  int sz = valid ? 8 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+// warp index as a warp-uniform value: lets the compiler keep the per-pair loops (and the shuffles inside) convergent
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------ forward
+// out[b, f, t] = Re X_t[f], out[b, F + f, t] = Im X_t[f],  X_t = rfft_N( window * reflect_pad(x)[t*hop : t*hop + win] )
+// Persistent CTAs walk the (utterance, tile of 32 frames) list; the next tile's samples stream into the other half of
+// a double buffer while this tile is transformed.
+__global__ void __launch_bounds__(THREADS, 2)
+stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict__ window, int win, int hop, int pad,
+                float* __restrict__ out, int T, int tiles, int total, int xs_cap) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* zbuf = reinterpret_cast<float2*>(smem_raw);                   // [TILE/2][ZPITCH]
+  float* xs = reinterpret_cast<float*>(zbuf + (TILE / 2) * ZPITCH);     // [2][xs_cap] staged samples
+  const int tid = threadIdx.x, lane = tid & 31, warp = uniform_warp_idx();
+  constexpr int F = NFFT / 2 + 1;
+
+  // stage a tile's samples once (each is used by ceil(win / hop) frames), mirroring at the clip ends
+  // (F.pad(mode='reflect'), conv_stft.py:55); the NFFT - win floats behind the last frame are zeroed so that the
+  // frame loads below need no bounds predicate (they are multiplied by a zero window tap)
+  auto stage = [&](int idx, float* dst) {
+    const int b = idx / tiles, t0 = (idx - b * tiles) * TILE;
+    const int nfr = min(TILE, T - t0);
+    const int nsamp = (nfr - 1) * hop + win;
+    const int64_t s0 = (int64_t)t0 * hop - pad;
+    const float* xb = x + (int64_t)b * L;
+    if (s0 >= 0 && s0 + nsamp <= L && ((reinterpret_cast<uintptr_t>(xb + s0) & 15) == 0)) {
+      const float* src = xb + s0;
+      const int n4 = nsamp >> 2;
+      for (int i = tid; i < n4; i += THREADS) cp_async16(dst + 4 * i, src + 4 * i);
+      if (tid < (nsamp & 3)) cp_async4(dst + 4 * n4 + tid, src + 4 * n4 + tid);
+    } else {
+      for (int i = tid; i < nsamp; i += THREADS) {
+        int64_t sidx = s0 + i;
+        if (sidx < 0) sidx = -sidx;
+        else if (sidx >= L) sidx = 2 * (L - 1) - sidx;
+        cp_async4(dst + i, xb + sidx);
+      }
+    }
+    if (tid < NFFT - win) dst[nsamp + tid] = 0.0f;
+    cp_async_commit();
+  };
+
+  int idx = blockIdx.x;
+  if (idx < total) stage(idx, xs);
+  float2 tw[16];
+  lane_twiddles(tw, lane);
+  float wl[16];                              // window taps of this lane, times the 1/2 of the pair separation
+  static_for<16>([&](auto n2_) {
+    constexpr int n2 = decltype(n2_)::value;
+    int n = lane + 32 * n2;
+    wl[n2] = n < win ? 0.5f * __ldg(window + n) : 0.0f;
+  });
+  const bool t_even = (T & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0;
+
+  for (int buf = 0; idx < total; idx += gridDim.x, buf ^= 1) {
+    const int b = idx / tiles, t0 = (idx - b * tiles) * TILE;
+    const int nfr = min(TILE, T - t0);
+    const float* xc = xs + buf * xs_cap;
+    cp_async_wait_all();
+    __syncthreads();                         // this tile's samples landed; everyone left the previous write-out
+    if (idx + (int)gridDim.x < total) stage(idx + gridDim.x, xs + (buf ^ 1) * xs_cap);
+
+    const int npairs = (nfr + 1) >> 1;
+    for (int p = warp; p < npairs; p += WARPS) {
+      const float* fa = xc + (2 * p) * hop + lane;
+      const bool has_b = 2 * p + 1 < nfr;
+      const float* fb = has_b ? fa + hop : fa;
+      float2 v[16];
+      static_for<16>([&](auto n2_) {
+        constexpr int n2 = decltype(n2_)::value;
+        v[n2] = make_float2(fa[32 * n2] * wl[n2], fb[32 * n2] * wl[n2]);
+      });
+      if (!has_b) static_for<16>([&](auto n2_) { v[decltype(n2_)::value].y = 0.0f; });
+      float2* row = zbuf + p * ZPITCH;
+      warp_fft512<false>(v, tw, row, lane);
+      const int h = lane >> 4, k2 = lane & 15;
+      static_for<16>([&](auto k_) {
+        constexpr int k = decltype(k_)::value;
+        row[16 * k + 256 * h + k2] = v[k];
+      });
+    }
+    __syncthreads();
+
+    // separate the two real spectra of each pair and write runs along t:  X_A[f] = (Z[f] + conj Z[N-f]) / 2,
+    // X_B[f] = (Z[f] - conj Z[N-f]) / 2i  (the 1/2 rode in on the window).  Half a warp covers one row f
+    // (16 pairs = up to 32 frames = 128 contiguous bytes); t0 is a multiple of 32, so with an even T every pair is an
+    // aligned float2.
+    const int p = lane & 15, fo = lane >> 4;
+    if (p < npairs) {
+      const bool has_b = 2 * p + 1 < nfr;
+      const float2* zr = zbuf + p * ZPITCH;
+      float* pre = out + (int64_t)b * (2 * F) * T + (t0 + 2 * p) + (int64_t)(2 * warp + fo) * T;
+      const int64_t im_off = (int64_t)F * T, step = (int64_t)(2 * WARPS) * T;
+      if (t_even && has_b) {
+#pragma unroll 4
+        for (int f = 2 * warp + fo; f < F; f += 2 * WARPS, pre += step) {
+          float2 z1 = zr[f], z2 = zr[(NFFT - f) & (NFFT - 1)];
+          *reinterpret_cast<float2*>(pre) = make_float2(z1.x + z2.x, z1.y + z2.y);
+          *reinterpret_cast<float2*>(pre + im_off) = make_float2(z1.y - z2.y, z2.x - z1.x);
+        }
+      } else {
+#pragma unroll 2
+        for (int f = 2 * warp + fo; f < F; f += 2 * WARPS, pre += step) {
+          float2 z1 = zr[f], z2 = zr[(NFFT - f) & (NFFT - 1)];
+          pre[0] = z1.x + z2.x;
+          pre[im_off] = z1.y - z2.y;
+          if (has_b) { pre[1] = z1.y + z2.y; pre[im_off + 1] = z2.x - z1.x; }
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ inverse
+// out[b, n - crop] = scale[n] * sum_t y_t[n - t*hop]   (conv_stft.py:101-114), y_t as in the file header.
+// One tile owns 32 hop blocks of the output and transforms the 32 + halo frames that reach them (the halo frames
+// are recomputed by the neighbouring tile: deterministic, no atomics, no second pass).  halo = J - 1 rounded up to
+// even, so that a tile's first frame is even and a pair of frames is one aligned 8-byte copy when T is even.
+__global__ void __launch_bounds__(THREADS, 2)
+istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict__ window, int win, int hop, int J,
+                 float c_even, float c_odd, const float* __restrict__ scale, int64_t crop, int64_t out_len,
+                 float* __restrict__ out, int Q, int pitch, int tiles, int total, unsigned hop_magic) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int F = NFFT / 2 + 1, C2 = 2 * F;
+  float* sbuf = reinterpret_cast<float*>(smem_raw);                        // [C2][pitch]: spectra, then frames
+  float2* scratch = reinterpret_cast<float2*>(sbuf + (size_t)C2 * pitch);  // [WARPS][16 * TPITCH]
+  const int tid = threadIdx.x, lane = tid & 31, warp = uniform_warp_idx();
+
+  float2 tw[16];
+  lane_twiddles(tw, lane);
+  const int h = lane >> 4, m2 = lane & 15;
+  float wl[16];
+  static_for<16>([&](auto k_) {
+    constexpr int k = decltype(k_)::value;
+    int m = 16 * k + 256 * h + m2;
+    wl[k] = m < win ? __ldg(window + m) * (1.0f / NFFT) : 0.0f;
+  });
+  const float cpar = (m2 & 1) ? c_odd : c_even;
+  const int hp = pitch >> 1;                                   // row pitch in float2 (odd)
+  float2* s2 = reinterpret_cast<float2*>(sbuf);
+  const int halo = (J - 1 + 1) & ~1;
+  const bool pair_copies = (T & 1) == 0 && (reinterpret_cast<uintptr_t>(spec) & 7) == 0;
+
+  for (int idx = blockIdx.x; idx < total; idx += gridDim.x) {
+    const int b = idx / tiles, q0 = (idx - b * tiles) * TILE;
+    const int nq = min(TILE, Q - q0);
+    const int tfirst = q0 - halo, nfr = nq + halo;
+    const int npairs = (nfr + 1) >> 1;
+    const float* sb = spec + (int64_t)b * C2 * T;
+
+    // stage spec[b, :, tfirst : tfirst + 2 npairs] (zero outside [0, T)); consecutive threads walk along t
+    if (pair_copies) {
+      int c = tid / npairs, pc = tid - c * npairs;
+      const int dc = THREADS / npairs, dp = THREADS - dc * npairs;
+      while (c < C2) {
+        int t = tfirst + 2 * pc;
+        bool ok = t >= 0 && t < T;
+        cp_async8(sbuf + c * pitch + 2 * pc, sb + (int64_t)c * T + (ok ? t : 0), ok);
+        c += dc; pc += dp;
+        if (pc >= npairs) { pc -= npairs; ++c; }
+      }
+    } else {
+      const int ncol = 2 * npairs;
+      int c = tid / ncol, tl = tid - c * ncol;
+      const int dc = THREADS / ncol, dt = THREADS - dc * ncol;
+      while (c < C2) {
+        int t = tfirst + tl;
+        bool ok = tl < nfr && t >= 0 && t < T;
+        cp_async4(sbuf + c * pitch + tl, sb + (int64_t)c * T + (ok ? t : 0), ok);
+        c += dc; tl += dt;
+        if (tl >= ncol) { tl -= ncol; ++c; }
+      }
+    }
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncthreads();
+
+    for (int p = warp; p < npairs; p += WARPS) {
+      // skip pairs whose frames both lie outside [0, T): their columns already hold zeros
+      int tA = tfirst + 2 * p;
+      if (tA + 1 < 0 || tA >= T) continue;
+      // G[f] = X_A[f] + i X_B[f] on the Hermitian-extended axis (times 2; DC and Nyquist real, counted once)
+      float2 v[16];
+      const float2* colp = s2 + p;
+      static_for<16>([&](auto f2_) {
+        constexpr int f2 = decltype(f2_)::value;
+        int g = f2 < 8 ? lane + 32 * f2 : NFFT - (lane + 32 * f2);     // f2 == 8, lane 0 -> Nyquist (g = 256)
+        float2 re = colp[g * hp];                                      // (Re X_A, Re X_B)
+        float2 im = colp[(F + g) * hp];                                // (Im X_A, Im X_B)
+        constexpr float sg = f2 < 8 ? 1.0f : -1.0f;
+        float2 gg = make_float2(re.x - sg * im.y, fmaf(sg, im.x, re.y));
+        if constexpr (f2 == 0 || f2 == 8) {
+          if (lane == 0) gg = make_float2(2.0f * re.x, 2.0f * re.y);
+        }
+        v[f2] = gg;
+      });
+      __syncwarp();
+      warp_fft512<true>(v, tw, scratch + warp * (16 * TPITCH), lane);
+      // rank-2 term of the truncated-DFT pseudo-inverse: subtract c_parity * (sum of this parity's samples below win)
+      float2 acc = make_float2(0.f, 0.f);
+      static_for<16>([&](auto k_) {
+        constexpr int k = decltype(k_)::value;
+        if (16 * k + 256 * h + m2 < win) acc = cadd(acc, v[k]);
+      });
+#pragma unroll
+      for (int off = 2; off <= 16; off <<= 1) {
+        acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off);
+        acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off);
+      }
+      acc.x *= cpar; acc.y *= cpar;
+      float2* ycol = s2 + p + (256 * h + m2) * hp;
+      static_for<16>([&](auto k_) {
+        constexpr int k = decltype(k_)::value;
+        if (16 * k + 256 * h + m2 < win)
+          ycol[16 * k * hp] = make_float2((v[k].x - acc.x) * wl[k], (v[k].y - acc.y) * wl[k]);
+      });
+    }
+    __syncthreads();
+
+    // overlap-add in a fixed order, normalise, crop:  sample n = q*hop + r sums frame q - j at offset j*hop + r.
+    // Frames outside [0, T) are skipped, not added as zeros: the partner of a real frame in a pair carries that
+    // frame's rounding noise, which the 1 / (window^2 + 1e-8) normaliser would amplify at un-centred clip edges.
+    float* ob = out + (int64_t)b * out_len;
+    const int total_s = nq * hop;
+    const int64_t n0 = (int64_t)q0 * hop;
+    const bool interior = q0 - (J - 1) >= 0 && q0 + nq <= T && J * hop == win && n0 >= crop &&
+                          n0 + total_s <= crop + out_len;
+    if (interior) {
+      for (int i = tid; i < total_s; i += THREADS) {
+        int ql = __umulhi((unsigned)i, hop_magic);           // i / hop
+        const float* col = sbuf + (i - ql * hop) * pitch + ql + halo;
+        float acc = col[0];
+        for (int j = 1; j < J; ++j) acc += col[j * (hop * pitch - 1)];
+        ob[n0 + i - crop] = scale ? acc * __ldg(scale + n0 + i) : acc;
+      }
+    } else {
+      for (int i = tid; i < total_s; i += THREADS) {
+        int ql = __umulhi((unsigned)i, hop_magic), r = i - ql * hop;
+        float acc = 0.0f;
+        for (int j = 0; j < J; ++j) {
+          int m = j * hop + r, t = q0 + ql - j;
+          if (m < win && t >= 0 && t < T) acc += sbuf[m * pitch + (ql - j + halo)];
+        }
+        int64_t n = n0 + i, pos = n - crop;
+        if (pos >= 0 && pos < out_len) ob[pos] = scale ? acc * __ldg(scale + n) : acc;
+      }
+    }
+    __syncthreads();                         // the next tile restages sbuf
+  }
+}
+
+bool fft_framing_ok(int win, int hop, int fft) {
+  return fft == NFFT && win >= 2 && win <= fft && hop >= 2 && hop <= 256 && (win + hop - 1) / hop <= MAXJ;
+}
+
+}  // namespace
+}  // namespace se
+
+extern "C" int se_stft_fft_supported(int win, int hop, int fft) { return se::fft_framing_ok(win, hop, fft) ? 1 : 0; }
+
+extern "C" int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
+                               int pad, float* out, int64_t T, void* stream) {
+  using namespace se;
+  SE_REQUIRE(x && window && out, "se_stft_fft_fwd: null pointer");
+  SE_REQUIRE(B >= 0 && L > 0 && T >= 0 && pad >= 0, "se_stft_fft_fwd: bad dims");
+  if (!fft_framing_ok(win, hop, fft))
+    return fail(SE_ERR_UNSUPPORTED, "se_stft_fft_fwd: win %d / hop %d / fft %d outside the FFT engine (fft 512, hop <= 256, "
+                                    "ceil(win/hop) <= %d)", win, hop, fft, MAXJ);
+  SE_REQUIRE(pad < L && (T - 1) * hop + win <= L + 2 * (int64_t)pad, "se_stft_fft_fwd: frames exceed the padded clip");
+  if (B == 0 || T == 0) return SE_OK;
+  int64_t tiles = (T + TILE - 1) / TILE;
+  SE_REQUIRE(T < (1 << 30) && tiles * B < (1ll << 31), "se_stft_fft_fwd: batch x frame count too large");
+  int xs_cap = ((TILE - 1) * hop + NFFT + 3) & ~3;
+  size_t smem = (size_t)(TILE / 2) * ZPITCH * sizeof(float2) + 2 * (size_t)xs_cap * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    SE_CUDA(cudaFuncSetAttribute(stft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024));
+    attr_set = true;
+  }
+  int total = (int)(tiles * B);
+  int grid = total < 2 * num_sms() ? total : 2 * num_sms();
+  stft_fft_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(x, L, window, win, hop, pad, out, (int)T, (int)tiles,
+                                                                 total, xs_cap);
+  return check_launch("se_stft_fft_fwd");
+}
+
+extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
+                                const float* scale, int64_t crop_front, int64_t out_len, float* out, void* stream) {
+  using namespace se;
+  SE_REQUIRE(spec && window && out, "se_istft_fft_fwd: null pointer");
+  SE_REQUIRE(B >= 0 && T >= 0 && crop_front >= 0 && out_len >= 0, "se_istft_fft_fwd: bad dims");
+  if (!fft_framing_ok(win, hop, fft))
+    return fail(SE_ERR_UNSUPPORTED, "se_istft_fft_fwd: win %d / hop %d / fft %d outside the FFT engine (fft 512, hop <= 256, "
+                                    "ceil(win/hop) <= %d)", win, hop, fft, MAXJ);
+  if (B == 0 || T == 0 || out_len == 0) return SE_OK;
+  int J = (win + hop - 1) / hop;
+  SE_REQUIRE(T < (1 << 30), "se_istft_fft_fwd: frame count too large");
+  int Q = (int)T + J - 1;
+  int64_t tiles = (Q + TILE - 1) / TILE;
+  SE_REQUIRE(tiles * B < (1ll << 31), "se_istft_fft_fwd: batch x frame count too large");
+  int halo = (J - 1 + 1) & ~1;
+  int npairs = (TILE + halo) / 2;
+  int pitch = 2 * (npairs | 1);                               // floats per row; pitch / 2 odd
+  size_t smem = (size_t)(fft + 2) * pitch * sizeof(float) + (size_t)WARPS * 16 * TPITCH * sizeof(float2);
+  static bool attr_set = false;
+  if (!attr_set) {
+    SE_CUDA(cudaFuncSetAttribute(istft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    attr_set = true;
+  }
+  // closed form of pinv for the first `win` rows of the real DFT:
+  // (K^T K)^-1 = (2/N) (I - e e^T / (N/2 + n_e) - o o^T / (N/2 + n_o))
+  float c_even = 1.0f / (float)(fft / 2 + (win + 1) / 2), c_odd = 1.0f / (float)(fft / 2 + win / 2);
+  int total = (int)(tiles * B);
+  int grid = total < 2 * num_sms() ? total : 2 * num_sms();
+  // i / hop for 0 <= i < 32 * 256 as __umulhi(i, magic): exact for these small dividends
+  unsigned hop_magic = hop == 1 ? 0xffffffffu : (unsigned)((0x100000000ull + (unsigned)hop - 1) / (unsigned)hop);
+  istft_fft_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(spec, (int)T, window, win, hop, J, c_even, c_odd, scale,
+                                                                  crop_front, out_len, out, Q, pitch, (int)tiles, total,
+                                                                  hop_magic);
+  return check_launch("se_istft_fft_fwd");
+}

@@ -18,7 +18,14 @@ from cases import STFT_CASES, CONV_CASES
 pytestmark = pytest.mark.gpu
 DEV = 'cuda:0'
 TOL_EXACT = 1e-5
-TOL_STFT = {'simt': 1e-5, 'umma': 3e-5}      # exact-fp32 SIMT kernels / bf16x3 tensor-core framing
+# exact-fp32 SIMT kernels / bf16x3 tensor-core framing / fp32 shared-memory FFT (fft 512 only)
+TOL_STFT = {'simt': 1e-5, 'umma': 3e-5, 'fft': 1e-5}
+ENGINES = ['simt', 'umma', 'fft']
+
+
+def _skip_unless_fft_covers(engine, win, hop, fft):
+    if engine == 'fft' and _abi.lib().se_stft_fft_supported(win, hop, fft) != 1:
+        pytest.skip(f'FFT engine does not cover {win}/{hop}/{fft}')
 
 
 def _stft_pair(engine, *args, **kw):
@@ -32,12 +39,13 @@ def _lib(built_lib):
     assert built_lib.se_device_ok() == 1, 'these tests need a compute-capability 10.x device'
 
 
-@pytest.mark.parametrize('engine', ['simt', 'umma'])
+@pytest.mark.parametrize('engine', ENGINES)
 @pytest.mark.parametrize('i', range(len(STFT_CASES)))
 def test_stft_istft_golden(i, engine):
     g = golden('stft')
     tol = TOL_STFT[engine]
     win, hop, fft, L = STFT_CASES[i]
+    _skip_unless_fft_covers(engine, win, hop, fft)
     x = rand((2, L), 100 + i, 0.1).to(DEV)
     st, ist = _stft_pair(engine, win, hop, fft)
     with torch.no_grad():
@@ -64,7 +72,7 @@ def test_stft_istft_golden(i, engine):
             assert rel_l2(ist(gm, gp).cpu(), g[f'{i}_wav_polar']) < tol
 
 
-@pytest.mark.parametrize('engine', ['simt', 'umma'])
+@pytest.mark.parametrize('engine', ENGINES)
 def test_stft_input_forms_and_not_centered(engine):
     g = golden('stft')
     tol = TOL_STFT[engine]
@@ -84,9 +92,10 @@ def test_stft_input_forms_and_not_centered(engine):
 
 @pytest.mark.parametrize('win,hop,fft,L,B', [(400, 100, 512, 64000, 8), (512, 128, 512, 64000, 8),
                                              (320, 160, 640, 64000, 4), (400, 100, 512, 160000, 2)])
-@pytest.mark.parametrize('engine', ['simt', 'umma'])
+@pytest.mark.parametrize('engine', ENGINES)
 def test_stft_full_size_vs_oracle(win, hop, fft, L, B, engine):
     tol = TOL_STFT[engine]
+    _skip_unless_fft_covers(engine, win, hop, fft)
     x = synth_noisy_speech(B, L, seed=3)
     st, ist = _stft_pair(engine, win, hop, fft)
     with torch.no_grad():
@@ -97,6 +106,52 @@ def test_stft_full_size_vs_oracle(win, hop, fft, L, B, engine):
         wav_ref = oracle.istft_ref(spec_ref, ist.weight.cpu(), ist.window.cpu(), hop, fft // 2)
         assert wav.shape == wav_ref.shape and rel_l2(wav.cpu(), wav_ref) < tol
         assert rel_l2(wav.cpu(), x[:, :wav.shape[1]]) < tol
+
+
+@pytest.mark.parametrize('win,hop,L,B,center', [(400, 100, 64000, 3, True), (512, 128, 37001, 2, True),
+                                                (320, 160, 5000, 5, True), (400, 100, 1311, 1, False),
+                                                (512, 64, 9000, 2, True), (37, 11, 2000, 2, True),
+                                                (400, 100, 700, 2, True), (512, 256, 8192, 2, False)])
+def test_stft_fft_engine_matches_exact_simt(win, hop, L, B, center):
+    """the FFT kernels against the exact-fp32 dense projection on ragged sizes: odd frame counts, clips shorter
+    than a tile, hop == win, tiny windows, eight overlapping frames, output_length crops"""
+    x = rand((B, L), 5, 0.3).to(DEV)
+    st, ist = _stft_pair('fft', win, hop, 512, center=center)
+    st0, ist0 = _stft_pair('simt', win, hop, 512, center=center)
+    with torch.no_grad():
+        spec, spec0 = st(x), st0(x)
+        assert spec.shape == spec0.shape and rel_l2(spec.cpu(), spec0.cpu()) < 2e-6
+        assert (spec[:, 257] == 0).all() and (spec[:, 513] == 0).all()       # Im of DC and Nyquist
+        sp = spec0 + 0.05 * torch.randn_like(spec0)                           # not a consistent STFT
+        for kw in ({}, {'output_length': L - 5}, {'output_length': 17}):
+            wav, wav0 = ist(sp, **kw), ist0(sp, **kw)
+            assert wav.shape == wav0.shape
+            interior = slice(hop, -hop) if not center and wav.shape[1] > 3 * hop else slice(None)
+            assert rel_l2(wav[:, interior].cpu(), wav0[:, interior].cpu()) < (5e-6 if center else 2e-5)
+
+
+def test_stft_fft_engine_only_for_the_dft_basis():
+    """`engine='auto'` takes the FFT kernels only when `weight` is the closed-form basis: a checkpoint with any other
+    basis keeps the dense projection (and its result), `engine='fft'` refuses it, fft sizes other than 512 too"""
+    x = rand((2, 4000), 9, 0.1).to(DEV)
+    st, ist = _stft_pair('auto', 400, 100, 512)
+    assert st._pick_engine('ConvSTFT', st.weight[0, 0], False) == 'fft'
+    assert ist._pick_engine('ConviSTFT', ist.window, True) == 'fft'
+    with torch.no_grad():
+        st.weight[40, 0, 7] += 1e-3
+        ist.weight[3, 0, 100] += 1e-4
+        assert st._pick_engine('ConvSTFT', st.weight[0, 0], False) == 'umma'
+        assert ist._pick_engine('ConviSTFT', ist.window, True) == 'umma'
+        spec = st(x)
+        ref = oracle.stft_ref(x.cpu(), st.weight.cpu(), 100, 256)
+        assert rel_l2(spec.cpu(), ref) < 3e-5
+        wav = ist(spec)
+        assert rel_l2(wav.cpu(), oracle.istft_ref(ref, ist.weight.cpu(), ist.window.cpu(), 100, 256)) < 3e-5
+        st.engine = 'fft'
+        with pytest.raises(RuntimeError):
+            st(x)
+    with pytest.raises(RuntimeError):
+        _stft_pair('fft', 320, 160, 640)[0](x)
 
 
 def _conv_case(i, engine):
