@@ -277,17 +277,36 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
 
 // ------------------------------------------------------------------------------------------------ inverse
 // out[b, n - crop] = scale[n] * sum_t y_t[n - t*hop]   (conv_stft.py:101-114), y_t as in the file header.
-// One tile owns 32 hop blocks of the output and transforms the 32 + halo frames that reach them (the halo frames
-// are recomputed by the neighbouring tile: deterministic, no atomics, no second pass).  halo = J - 1 rounded up to
-// even, so that a tile's first frame is even and a pair of frames is one aligned 8-byte copy when T is even.
+// One tile owns `tq` = 32 - halo hop blocks of the output and transforms the 32 frames (16 pairs: two full rounds
+// of the 8 warps) that reach them; the halo frames are recomputed by the neighbouring tile: deterministic, no
+// atomics, no second pass.  halo = J - 1 rounded up to even, so that a tile's first frame is even and a pair of
+// frames is one aligned 8-byte copy when T is even.
+constexpr int IPAIRS = TILE / 2;            // frame pairs per tile
+constexpr int IPITCH = 2 * (IPAIRS | 1);    // floats per spectrum row in shared memory; IPITCH / 2 odd
+
+// interior tiles: every frame exists, every tap is below `win`, every sample is inside the crop
+template <int JJ>
+__device__ __forceinline__ void ola_interior(const float* sbuf, int total_s, int hop, int halo, unsigned hop_magic,
+                                             const float* __restrict__ scale, float* __restrict__ dst, int tid) {
+  const int jstep = hop * IPITCH - 1;
+  for (int i = tid; i < total_s; i += THREADS) {
+    int ql = __umulhi((unsigned)i, hop_magic);           // i / hop
+    const float* col = sbuf + (i - ql * hop) * IPITCH + ql + halo;
+    float acc = col[0];
+#pragma unroll
+    for (int j = 1; j < JJ; ++j) acc += col[j * jstep];
+    dst[i] = acc * __ldg(scale + i);
+  }
+}
+
 __global__ void __launch_bounds__(THREADS, 2)
 istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict__ window, int win, int hop, int J,
                  float c_even, float c_odd, const float* __restrict__ scale, int64_t crop, int64_t out_len,
-                 float* __restrict__ out, int Q, int pitch, int tiles, int total, unsigned hop_magic) {
+                 float* __restrict__ out, int Q, int tq, int tiles, int total, unsigned hop_magic) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int F = NFFT / 2 + 1, C2 = 2 * F;
-  float* sbuf = reinterpret_cast<float*>(smem_raw);                        // [C2][pitch]: spectra, then frames
-  float2* scratch = reinterpret_cast<float2*>(sbuf + (size_t)C2 * pitch);  // [WARPS][16 * TPITCH]
+  float* sbuf = reinterpret_cast<float*>(smem_raw);                         // [C2][IPITCH]: spectra, then frames
+  float2* scratch = reinterpret_cast<float2*>(sbuf + (size_t)C2 * IPITCH);  // [WARPS][16 * TPITCH]
   const int tid = threadIdx.x, lane = tid & 31, warp = uniform_warp_idx();
 
   float2 tw[16];
@@ -300,39 +319,39 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
     wl[k] = m < win ? __ldg(window + m) * (1.0f / NFFT) : 0.0f;
   });
   const float cpar = (m2 & 1) ? c_odd : c_even;
-  const int hp = pitch >> 1;                                   // row pitch in float2 (odd)
+  constexpr int hp = IPITCH >> 1;                              // row pitch in float2 (odd)
   float2* s2 = reinterpret_cast<float2*>(sbuf);
   const int halo = (J - 1 + 1) & ~1;
   const bool pair_copies = (T & 1) == 0 && (reinterpret_cast<uintptr_t>(spec) & 7) == 0;
 
   for (int idx = blockIdx.x; idx < total; idx += gridDim.x) {
-    const int b = idx / tiles, q0 = (idx - b * tiles) * TILE;
-    const int nq = min(TILE, Q - q0);
+    const int b = idx / tiles, q0 = (idx - b * tiles) * tq;
+    const int nq = min(tq, Q - q0);
     const int tfirst = q0 - halo, nfr = nq + halo;
     const int npairs = (nfr + 1) >> 1;
     const float* sb = spec + (int64_t)b * C2 * T;
 
-    // stage spec[b, :, tfirst : tfirst + 2 npairs] (zero outside [0, T)); consecutive threads walk along t
+    // stage spec[b, :, tfirst : tfirst + 2 npairs] (zero outside [0, T)): half a warp per spectrum row (16 pairs =
+    // 128 contiguous bytes), lanes along t
     if (pair_copies) {
-      int c = tid / npairs, pc = tid - c * npairs;
-      const int dc = THREADS / npairs, dp = THREADS - dc * npairs;
-      while (c < C2) {
-        int t = tfirst + 2 * pc;
-        bool ok = t >= 0 && t < T;
-        cp_async8(sbuf + c * pitch + 2 * pc, sb + (int64_t)c * T + (ok ? t : 0), ok);
-        c += dc; pc += dp;
-        if (pc >= npairs) { pc -= npairs; ++c; }
+      const int pc = lane & 15, c0 = 2 * warp + (lane >> 4);
+      const int t = tfirst + 2 * pc;
+      const bool ok = t >= 0 && t < T;                         // T and t even: both frames of the pair exist or neither
+      if (pc < npairs) {
+        const float* src = sb + (int64_t)c0 * T + (ok ? t : 0);
+        float* dst = sbuf + c0 * IPITCH + 2 * pc;
+#pragma unroll 4
+        for (int c = c0; c < C2; c += 2 * WARPS, src += (int64_t)(2 * WARPS) * T, dst += 2 * WARPS * IPITCH)
+          cp_async8(dst, src, ok);
       }
     } else {
-      const int ncol = 2 * npairs;
-      int c = tid / ncol, tl = tid - c * ncol;
-      const int dc = THREADS / ncol, dt = THREADS - dc * ncol;
-      while (c < C2) {
-        int t = tfirst + tl;
-        bool ok = tl < nfr && t >= 0 && t < T;
-        cp_async4(sbuf + c * pitch + tl, sb + (int64_t)c * T + (ok ? t : 0), ok);
-        c += dc; tl += dt;
-        if (tl >= ncol) { tl -= ncol; ++c; }
+      const int t = tfirst + lane;
+      const bool ok = lane < nfr && t >= 0 && t < T;
+      if (lane < 2 * npairs) {
+        const float* src = sb + (int64_t)warp * T + (ok ? t : 0);
+        float* dst = sbuf + warp * IPITCH + lane;
+#pragma unroll 4
+        for (int c = warp; c < C2; c += WARPS, src += (int64_t)WARPS * T, dst += WARPS * IPITCH) cp_async4(dst, src, ok);
       }
     }
     cp_async_commit();
@@ -372,11 +391,11 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
         acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off);
       }
       acc.x *= cpar; acc.y *= cpar;
+      // rows >= win get zeros (their window tap is 0); the overlap-add never reads them
       float2* ycol = s2 + p + (256 * h + m2) * hp;
       static_for<16>([&](auto k_) {
         constexpr int k = decltype(k_)::value;
-        if (16 * k + 256 * h + m2 < win)
-          ycol[16 * k * hp] = make_float2((v[k].x - acc.x) * wl[k], (v[k].y - acc.y) * wl[k]);
+        ycol[16 * k * hp] = make_float2((v[k].x - acc.x) * wl[k], (v[k].y - acc.y) * wl[k]);
       });
     }
     __syncthreads();
@@ -388,22 +407,16 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
     const int total_s = nq * hop;
     const int64_t n0 = (int64_t)q0 * hop;
     const bool interior = q0 - (J - 1) >= 0 && q0 + nq <= T && J * hop == win && n0 >= crop &&
-                          n0 + total_s <= crop + out_len;
-    if (interior) {
-      for (int i = tid; i < total_s; i += THREADS) {
-        int ql = __umulhi((unsigned)i, hop_magic);           // i / hop
-        const float* col = sbuf + (i - ql * hop) * pitch + ql + halo;
-        float acc = col[0];
-        for (int j = 1; j < J; ++j) acc += col[j * (hop * pitch - 1)];
-        ob[n0 + i - crop] = scale ? acc * __ldg(scale + n0 + i) : acc;
-      }
-    } else {
+                          n0 + total_s <= crop + out_len && scale != nullptr;
+    if (interior && J == 4) ola_interior<4>(sbuf, total_s, hop, halo, hop_magic, scale + n0, ob + (n0 - crop), tid);
+    else if (interior && J == 2) ola_interior<2>(sbuf, total_s, hop, halo, hop_magic, scale + n0, ob + (n0 - crop), tid);
+    else {
       for (int i = tid; i < total_s; i += THREADS) {
         int ql = __umulhi((unsigned)i, hop_magic), r = i - ql * hop;
         float acc = 0.0f;
         for (int j = 0; j < J; ++j) {
           int m = j * hop + r, t = q0 + ql - j;
-          if (m < win && t >= 0 && t < T) acc += sbuf[m * pitch + (ql - j + halo)];
+          if (m < win && t >= 0 && t < T) acc += sbuf[m * IPITCH + (ql - j + halo)];
         }
         int64_t n = n0 + i, pos = n - crop;
         if (pos >= 0 && pos < out_len) ob[pos] = scale ? acc * __ldg(scale + n) : acc;
@@ -460,15 +473,14 @@ extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const f
   int J = (win + hop - 1) / hop;
   SE_REQUIRE(T < (1 << 30), "se_istft_fft_fwd: frame count too large");
   int Q = (int)T + J - 1;
-  int64_t tiles = (Q + TILE - 1) / TILE;
-  SE_REQUIRE(tiles * B < (1ll << 31), "se_istft_fft_fwd: batch x frame count too large");
   int halo = (J - 1 + 1) & ~1;
-  int npairs = (TILE + halo) / 2;
-  int pitch = 2 * (npairs | 1);                               // floats per row; pitch / 2 odd
-  size_t smem = (size_t)(fft + 2) * pitch * sizeof(float) + (size_t)WARPS * 16 * TPITCH * sizeof(float2);
+  int tq = TILE - halo;                                       // hop blocks of output per tile (32 frames with the halo)
+  int64_t tiles = (Q + tq - 1) / tq;
+  SE_REQUIRE(tiles * B < (1ll << 31), "se_istft_fft_fwd: batch x frame count too large");
+  size_t smem = (size_t)(fft + 2) * IPITCH * sizeof(float) + (size_t)WARPS * 16 * TPITCH * sizeof(float2);
   static bool attr_set = false;
   if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute(istft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    SE_CUDA(cudaFuncSetAttribute(istft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set = true;
   }
   // closed form of pinv for the first `win` rows of the real DFT:
@@ -477,9 +489,9 @@ extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const f
   int total = (int)(tiles * B);
   int grid = total < 2 * num_sms() ? total : 2 * num_sms();
   // i / hop for 0 <= i < 32 * 256 as __umulhi(i, magic): exact for these small dividends
-  unsigned hop_magic = hop == 1 ? 0xffffffffu : (unsigned)((0x100000000ull + (unsigned)hop - 1) / (unsigned)hop);
+  unsigned hop_magic = (unsigned)((0x100000000ull + (unsigned)hop - 1) / (unsigned)hop);
   istft_fft_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(spec, (int)T, window, win, hop, J, c_even, c_odd, scale,
-                                                                  crop_front, out_len, out, Q, pitch, (int)tiles, total,
+                                                                  crop_front, out_len, out, Q, tq, (int)tiles, total,
                                                                   hop_magic);
   return check_launch("se_istft_fft_fwd");
 }
