@@ -200,7 +200,7 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
         cp_async4(dst + i, xb + sidx);
       }
     }
-    if (tid < NFFT - win) dst[nsamp + tid] = 0.0f;
+    for (int i = tid; i < NFFT - win; i += THREADS) dst[nsamp + i] = 0.0f;
     cp_async_commit();
   };
 

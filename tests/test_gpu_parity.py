@@ -399,7 +399,7 @@ def test_dcunet_frcrn_fused_chain_matches_modular_path_and_oracle(cls, args, L):
             assert rel_l2(torch.clamp(ours.istft(spec_a.contiguous()), -1, 1).cpu(), wav_a.cpu()) < 1e-6
             assert rel_l2(torch.clamp(ours.istft(spec_fix.contiguous()), -1, 1).cpu(), wav_b.cpu()) < tol
 
-        agree(spec_f, wav_f, spec_m, wav_m, 1e-4)
+        agree(spec_f, wav_f, spec_m, wav_m, 2e-4)
         agree(spec_f, wav_f, spec_ref, wav_ref, 3e-4)
         agree(spec_m, wav_m, spec_ref, wav_ref, 3e-4)
 
