@@ -12,6 +12,24 @@ __device__ __forceinline__ void mag_phase(float re, float im, float& mag, float&
   ph = atan2f(im, re);
 }
 
+// (cos, sin) of atan2(im, re) without the transcendental round trip: the unit vector (re, im) / |(re, im)|.
+// Exactly-zero, denormal-scale and huge inputs take the reference's own atan2 -> sincos route (signed zeros and
+// the atan2(0, 0) = 0 convention included); the branch is warp-divergent only on such bins.
+__device__ __forceinline__ void unit_dir(float re, float im, float& c, float& s) {
+  const float d2 = re * re + im * im;
+  if (d2 > 1e-30f && d2 < 1e30f) {
+    const float r = rsqrtf(d2);
+    c = re * r; s = im * r;
+  } else {
+    sincosf(atan2f(im, re), &s, &c);
+  }
+}
+
+// The polar masks are evaluated in rectangular form:  mag * (cos, sin)(a + b) is the complex product of the unit
+// vectors of a and b, so DCCRN-E needs no atan2 / sincos at all (the reference's eps sits only inside the two
+// magnitudes, _2008_00264_dccrn.py:210, and is kept there) and DCUNet's bounded-tanh needs one atan2 + one sincos
+// for its angle / magnitude quirk (_1903_03107_dcunet.py:177).  ~60 instead of ~250 instructions per bin: the
+// kernel is HBM-bound instead of SFU/issue-bound.
 template <int KIND>
 __device__ __forceinline__ void mask_eval(float nr, float ni, float mr, float mi, float& re, float& im) {
   if (KIND == SE_MASK_DCCRN_R || KIND == SE_MASK_DCUNET_UNB) {
@@ -25,79 +43,61 @@ __device__ __forceinline__ void mask_eval(float nr, float ni, float mr, float mi
   } else if (KIND == SE_MASK_FRCRN) {
     re = tanhf(mr) * nr; im = tanhf(mi) * ni;
   } else {
-    float n_mag, n_ph, m_mag, m_ph;
-    mag_phase(nr, ni, n_mag, n_ph);
-    mag_phase(mr, mi, m_mag, m_ph);
-    if (KIND == SE_MASK_DCCRN_E) m_ph = atan2f(mi / m_mag, mr / m_mag);   // dccrn.py:198-202
-    else                          m_ph = m_ph / m_mag;                     // dcunet.py:177
-    float g = n_mag * tanhf(m_mag), s, c;
-    sincosf(n_ph + m_ph, &s, &c);
-    re = g * c; im = g * s;
+    const float n_mag = sqrtf(nr * nr + ni * ni + 1e-8f), m_mag = sqrtf(mr * mr + mi * mi + 1e-8f);
+    float cn, sn, cm, sm;
+    unit_dir(nr, ni, cn, sn);                                              // noisy phase
+    if (KIND == SE_MASK_DCCRN_E) unit_dir(mr / m_mag, mi / m_mag, cm, sm); // dccrn.py:198-202 (scale invariant)
+    else sincosf(atan2f(mi, mr) / m_mag, &sm, &cm);                        // dcunet.py:177: angle / magnitude
+    const float g = n_mag * tanhf(m_mag);
+    re = g * (cn * cm - sn * sm); im = g * (cn * sm + sn * cm);
   }
 }
 
-// grid: (ceil(T / (blockDim*4)), rows = B*F); each thread handles 4 t's strided by blockDim
+// one warp per (b, f) row: lanes walk t in 128-byte runs, four runs (16 loads) in flight per lane
 template <int KIND>
-__global__ void __launch_bounds__(128)
-mask_kernel(Plane nr, Plane ni, Plane mr, Plane mi, int F, int64_t T, float* __restrict__ out) {
-  const int64_t row = blockIdx.y;
+__global__ void __launch_bounds__(256)
+mask_kernel(Plane nr, Plane ni, Plane mr, Plane mi, int64_t rows, int F, int64_t T, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
   const int64_t b = row / F; const int f = (int)(row - b * F);
   const float* pnr = nr.p + b * nr.bs + f * nr.fs;
   const float* pni = ni.p + b * ni.bs + f * ni.fs;
   float* ore = out + (b * 2 * F + f) * T;
   float* oim = ore + (int64_t)F * T;
-  const int64_t t0 = (int64_t)blockIdx.x * (blockDim.x * 4) + threadIdx.x;
   if (KIND == SE_MASK_FRCRN && f < 2) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      int64_t t = t0 + j * blockDim.x;
-      if (t < T) { ore[t] = 0.f; oim[t] = 0.f; }
-    }
+    for (int64_t t = lane; t < T; t += 32) { ore[t] = 0.f; oim[t] = 0.f; }
     return;
   }
   const int fm = KIND == SE_MASK_FRCRN ? f - 2 : f;
   const float* pmr = mr.p + b * mr.bs + fm * mr.fs;
   const float* pmi = mi.p + b * mi.bs + fm * mi.fs;
-  float a[4], c[4], d[4], e[4];
+  for (int64_t t0 = lane; t0 < T; t0 += 128) {
+    float a[4], c[4], d[4], e[4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    int64_t t = t0 + j * blockDim.x;
-    bool ok = t < T;
-    a[j] = ok ? __ldg(pnr + t) : 0.f; c[j] = ok ? __ldg(pni + t) : 0.f;
-    d[j] = ok ? __ldg(pmr + t) : 1.f; e[j] = ok ? __ldg(pmi + t) : 0.f;
-  }
+    for (int j = 0; j < 4; ++j) {
+      const int64_t t = t0 + 32 * j;
+      const bool ok = t < T;
+      a[j] = ok ? __ldg(pnr + t) : 0.f; c[j] = ok ? __ldg(pni + t) : 0.f;
+      d[j] = ok ? __ldg(pmr + t) : 1.f; e[j] = ok ? __ldg(pmi + t) : 0.f;
+    }
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    int64_t t = t0 + j * blockDim.x;
-    float re, im;
-    mask_eval<KIND>(a[j], c[j], d[j], e[j], re, im);
-    if (t < T) { ore[t] = re; oim[t] = im; }
+    for (int j = 0; j < 4; ++j) {
+      const int64_t t = t0 + 32 * j;
+      float re, im;
+      mask_eval<KIND>(a[j], c[j], d[j], e[j], re, im);
+      if (t < T) { ore[t] = re; oim[t] = im; }
+    }
   }
 }
 
 template <int KIND>
 int launch_mask(Plane nr, Plane ni, Plane mr, Plane mi, int64_t B, int F, int64_t T, float* out,
                 cudaStream_t s) {
-  int64_t rows = B * F;
-  // rows go on grid.y (max 65535); larger problems are split along the batch below
-  if (rows <= 65535) {
-    dim3 grid((unsigned)((T + 511) / 512), (unsigned)rows);
-    mask_kernel<KIND><<<grid, 128, 0, s>>>(nr, ni, mr, mi, F, T, out);
-    return check_launch("se_mask_fwd");
-  }
-  // split along the batch so each launch has <= 65535 rows
-  int64_t bper = 65535 / F;
-  if (bper < 1) return fail(SE_ERR_UNSUPPORTED, "se_mask_fwd: F too large");
-  for (int64_t b0 = 0; b0 < B; b0 += bper) {
-    int64_t nb = B - b0 < bper ? B - b0 : bper;
-    Plane a = {nr.p + b0 * nr.bs, nr.bs, nr.fs}, c = {ni.p + b0 * ni.bs, ni.bs, ni.fs};
-    Plane d = {mr.p + b0 * mr.bs, mr.bs, mr.fs}, e = {mi.p + b0 * mi.bs, mi.bs, mi.fs};
-    dim3 grid((unsigned)((T + 511) / 512), (unsigned)(nb * F));
-    mask_kernel<KIND><<<grid, 128, 0, s>>>(a, c, d, e, F, T, out + b0 * 2 * F * T);
-    int rc = check_launch("se_mask_fwd");
-    if (rc != SE_OK) return rc;
-  }
-  return SE_OK;
+  const int64_t rows = B * F, blocks = (rows + 7) / 8;
+  if (blocks > 0x7fffffffll) return fail(SE_ERR_UNSUPPORTED, "se_mask_fwd: B*F too large");
+  mask_kernel<KIND><<<(unsigned)blocks, 256, 0, s>>>(nr, ni, mr, mi, rows, F, T, out);
+  return check_launch("se_mask_fwd");
 }
 
 // ---- backward: (d re, d im) -> gradients of the four input planes, same strided inputs --------

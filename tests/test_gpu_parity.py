@@ -280,6 +280,31 @@ def test_masks_golden_and_strided_inputs():
     assert rel_l2(SF.polar_to_rect(mags.to(DEV), ph.to(DEV)).cpu(), oracle.polar_to_rect_ref(mags, ph)) < TOL_EXACT
 
 
+def test_polar_masks_edge_values_match_the_atan2_route():
+    """the polar masks are evaluated in rectangular form (unit vectors instead of atan2 -> sincos); exact zeros,
+    signed zeros, denormal-scale and huge bins must still give what the reference's atan2 route gives"""
+    vals = torch.tensor([0.0, -0.0, 1e-25, -1e-25, 3e-20, 1e-4, -0.3, 1.0, -2.5, 7.0, 1e18, -1e18])
+
+    def planes(mvals_r, mvals_i):
+        g = torch.stack(torch.meshgrid(vals, vals, mvals_r, mvals_i, indexing='ij'), 0).reshape(4, 1, -1, 1)
+        return g.expand(4, 1, g.shape[2], 3).contiguous()
+
+    # DCUNet's angle / magnitude quirk amplifies a 1-ulp atan2 difference by 1 / |mask|: keep its masks O(1)
+    big = torch.tensor([-0.3, 1.0, -2.5, 7.0])
+    for fn, ref, (nr, ni, mr, mi) in (
+            (lambda *a: SF.mask_dccrn('E', *a), lambda *a: oracle.mask_dccrn_ref('E', *a), planes(vals[2:10], vals[1:9])),
+            (lambda *a: SF.mask_dcunet('bounded_tanh', *a), lambda *a: OPS.mask_dcunet('bounded_tanh', *a), planes(big, big))):
+        out = fn(nr.to(DEV), ni.to(DEV), mr.to(DEV), mi.to(DEV)).cpu()
+        want = torch.as_tensor(ref(nr, ni, mr, mi))
+        assert out.shape == want.shape and torch.isfinite(want).all() and torch.isfinite(out).all()
+        # error of each complex bin relative to that bin's magnitude (a component that is ~0 by cancellation has no
+        # relative accuracy of its own in either route)
+        f = want.shape[1] // 2
+        mag = (want[:, :f] ** 2 + want[:, f:] ** 2).sqrt()
+        err = ((out[:, :f] - want[:, :f]) ** 2 + (out[:, f:] - want[:, f:]) ** 2).sqrt() / (mag + 1e-9)
+        assert err.max() < 2e-5, err.max()
+
+
 MODELS = [('dccrn_cl', callers.DCCRN, ('dccrn-CL', 400, 100, 512)),
           ('dccrn_c', callers.DCCRN, ('dccrn-C', 400, 100, 512)),
           ('dcunet20', callers.DCUNet, ('dcunet20', 512, 128, 512)),
