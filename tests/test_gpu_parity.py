@@ -452,7 +452,8 @@ def test_cl2_roundtrip_and_two_source_block():
 
 @pytest.mark.parametrize('proj', ['torch', 'umma'])
 @pytest.mark.parametrize('N,T,cin,hid,layers,batch_first', [(6, 37, 64, 256, 1, True), (3, 20, 128, 256, 2, True),
-                                                            (5, 11, 32, 128, 1, False), (300, 9, 64, 256, 1, True)])
+                                                            (5, 11, 32, 128, 1, False), (300, 9, 64, 256, 1, True),
+                                                            (51, 7, 64, 256, 1, True), (31, 7, 64, 256, 2, True)])
 def test_complex_lstm_recurrent_kernel_vs_torch(N, T, cin, hid, layers, batch_first, proj):
     """csrc/lstm_rec.cu (+ the input projections on the GEMM engine for proj='umma') against torch's own
     fp32 LSTM on the CPU (the reference's arithmetic) and against cuDNN."""
