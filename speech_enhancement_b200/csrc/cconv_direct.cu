@@ -101,6 +101,126 @@ cconv_small_cin_kernel(const SmallCinParams p) {
   }
 }
 
+// Compile-time-shaped version for the first encoder layer of the three complex families (2 input channels; 5x2
+// stride 2x1 in DCCRN / FRCRN, 3x3 stride 1 in DCUNet): every tap loop unrolls, the K input samples of a pixel are
+// loaded once into registers and reused by each 32-channel pass, bias + leaky + the bf16 hi|lo split cost ~5
+// instructions per channel (packed cvt.rn.bf16x2), and CL2 pad channels are plain zero stores.  The generic kernel
+// above spends ~4x the FMA count in index arithmetic (profiles/r1e_hbm_full_summary.txt: 466 M instructions for
+// 110 M FFMAs).
+__device__ __forceinline__ void st_global_v8(void* ptr, const uint32_t* v) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+               "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
+template <int KH, int KW, int SH, int SW>
+__global__ void __launch_bounds__(128)
+cconv_first_kernel(const SmallCinParams p) {
+  constexpr int CIN2 = 2, K = CIN2 * KH * KW;
+  extern __shared__ float w_s[];                  // [K][Cr] weights, then [Cr] bias
+  const int Cr = (p.Cout2 + 31) / 32 * 32;
+  float* b_s = w_s + K * Cr;
+  for (int i = threadIdx.x; i < K * Cr; i += blockDim.x) {
+    int k = i / Cr, co = i - k * Cr;
+    w_s[i] = co < p.Cout2 ? __ldg(p.w + (int64_t)co * K + k) : 0.f;
+  }
+  for (int i = threadIdx.x; i < Cr; i += blockDim.x) b_s[i] = (i < p.Cout2 && p.bias != nullptr) ? __ldg(p.bias + i) : 0.f;
+  __syncthreads();
+  // 128 consecutive output pixels of one image per block (rows are not padded to the block size)
+  const int64_t plane = (int64_t)p.Ho * p.Wo;
+  const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t b = blockIdx.y;
+  if (pix >= plane) return;
+  const int ho = (int)(pix / p.Wo), wo = (int)(pix - (int64_t)ho * p.Wo);
+
+  float xk[K];
+  {
+    const int h0 = ho * SH - p.ph - p.pad_top, w0 = wo * SW - p.pw - p.pad_left;
+    const float* xb = p.x + b * p.xs_b;
+#pragma unroll
+    for (int c = 0; c < CIN2; ++c)
+#pragma unroll
+      for (int dh = 0; dh < KH; ++dh) {
+        const int h = h0 + dh;
+        const bool h_ok = h >= 0 && h < p.H;
+        const float* xr = xb + c * p.xs_c + (int64_t)h * p.xs_h + w0;
+#pragma unroll
+        for (int dw = 0; dw < KW; ++dw) {
+          const int w = w0 + dw;
+          xk[(c * KH + dh) * KW + dw] = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + dw) : 0.f;
+        }
+      }
+  }
+  const float slope = p.slope;
+  __nv_bfloat16* cb = p.y_cl2 != nullptr ? p.y_cl2 + (b * 2 * plane + pix) * p.y_Cp : nullptr;
+  for (int c0 = 0; c0 < Cr; c0 += 32) {
+    float acc[32];
+    {
+      const float4* br = reinterpret_cast<const float4*>(b_s + c0);
+#pragma unroll
+      for (int j4 = 0; j4 < 8; ++j4) {
+        const float4 b4 = br[j4];
+        acc[4 * j4] = b4.x; acc[4 * j4 + 1] = b4.y; acc[4 * j4 + 2] = b4.z; acc[4 * j4 + 3] = b4.w;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const float4* wr = reinterpret_cast<const float4*>(w_s + k * Cr + c0);
+#pragma unroll
+      for (int j4 = 0; j4 < 8; ++j4) {
+        const float4 w4 = wr[j4];
+        acc[4 * j4 + 0] = fmaf(w4.x, xk[k], acc[4 * j4 + 0]);
+        acc[4 * j4 + 1] = fmaf(w4.y, xk[k], acc[4 * j4 + 1]);
+        acc[4 * j4 + 2] = fmaf(w4.z, xk[k], acc[4 * j4 + 2]);
+        acc[4 * j4 + 3] = fmaf(w4.w, xk[k], acc[4 * j4 + 3]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) acc[j] = acc[j] > 0.f ? acc[j] : acc[j] * slope;
+    if (p.y != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc[j];
+    }
+    if (cb != nullptr) {
+      // channels >= Cout2 inside this pass carry zero weights and zero bias: they come out as exact zeros
+      uint32_t hi[16], lo[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+        const float2 hf = __bfloat1622float2(h2);
+        const __nv_bfloat162 l2 = __floats2bfloat162_rn(acc[2 * j] - hf.x, acc[2 * j + 1] - hf.y);
+        hi[j] = *reinterpret_cast<const uint32_t*>(&h2);
+        lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
+      }
+      // 32-byte stores: one full sector per lane and instruction (lanes are a pixel = 128+ bytes apart)
+      __nv_bfloat16* dh = cb + c0;
+      __nv_bfloat16* dl = cb + plane * p.y_Cp + c0;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        st_global_v8(dh + 16 * j, hi + 8 * j);
+        st_global_v8(dl + 16 * j, lo + 8 * j);
+      }
+    }
+  }
+  if (cb != nullptr) {                             // CL2 pad channels [Cr, y_Cp)
+    const uint32_t z[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    for (int c0 = Cr; c0 < p.y_Cp; c0 += 16) {       // Cr and y_Cp are multiples of 32
+      st_global_v8(cb + c0, z);
+      st_global_v8(cb + plane * p.y_Cp + c0, z);
+    }
+  }
+}
+
+template <int KH, int KW, int SH, int SW>
+static int launch_first(const SmallCinParams& p, int64_t B, cudaStream_t s) {
+  const int Cr = (p.Cout2 + 31) / 32 * 32;
+  const int smem = (2 * KH * KW * Cr + Cr) * 4;
+  dim3 grid((unsigned)(((int64_t)p.Ho * p.Wo + 127) / 128), (unsigned)B);
+  cconv_first_kernel<KH, KW, SH, SW><<<grid, 128, smem, s>>>(p);
+  return check_launch("se_cconv_small_cin(first)");
+}
+
 }  // namespace se
 
 extern "C" int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, int64_t xs_h, int64_t B, int Cin2,
@@ -121,6 +241,11 @@ extern "C" int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, in
   if (Ho > 65535 || B > 65535) return se::fail(SE_ERR_UNSUPPORTED, "se_cconv_small_cin: tensor too large");
   se::SmallCinParams p{x, xs_b, xs_c, xs_h, Cin2, H, W, pad_top, pad_left, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo,
                        packed, bias, slope, y_nchw, reinterpret_cast<__nv_bfloat16*>(y_cl2), y_Cp};
+  // the first encoder layers of DCCRN / FRCRN (5x2, stride 2x1) and DCUNet (3x3, stride 1): compile-time-shaped kernel
+  if (Cin2 == 2 && Cout2 >= 16 && Cout2 <= 256) {
+    if (kh == 5 && kw == 2 && sh == 2 && sw == 1) return se::launch_first<5, 2, 2, 1>(p, B, (cudaStream_t)stream);
+    if (kh == 3 && kw == 3 && sh == 1 && sw == 1) return se::launch_first<3, 3, 1, 1>(p, B, (cudaStream_t)stream);
+  }
   const int smem = K * Cr * 4;
   static int smem_attr = 48 * 1024;
   if (smem > smem_attr) {                         // only the 32-wide pass can exceed the default
