@@ -442,14 +442,17 @@ def run_ours(args):
     roofline = {'bound': 'tensor', 'kernel': f'complex conv stack ({len(st.events.get("cconv", [])) // nprof} conv launches per step)',
                 'achieved': tflops, 'peak': pk['bf16_tflops_sustained'], 'unit': 'TFLOP/s',
                 'frac': tflops / pk['bf16_tflops_sustained'],
-                # dram__bytes_read + write summed over the 11 conv GEMM launches of one step, from the ncu --set full
-                # capture profiles/r1c_gemm_full_summary.txt (B=64: 25.46 GB), scaled per utterance
+                # dram__bytes_read + write summed over the 11 conv GEMM launches of one step from the ncu --set full
+                # captures (profiles/r1c_gemm_full_summary.txt, B=64: 25.46 GB; the eight launches re-captured in
+                # profiles/r1e_gemm_full_summary.txt agree within 2 %), scaled per utterance
                 'traffic': 25.458e9 / 64 * B if args.model == 'dccrn' else None,
                 'traffic_unit': 'B per step (all conv GEMM launches)',
                 'peak_source': pk['source'] + ' bf16 dense (sustained)',
                 'note': f'algorithmic FLOPs ({MODEL["conv_gflop"]} GFLOP/utt); the tensor engine issues 3 bf16 passes per product'}
 
     cpu_val, cores, cpu_sec = time_cpu_oracle(2, iters=5, warmup=1)
+    stages['stft_engine'] = model.stft._pick_engine('ConvSTFT', model.stft.weight[0, 0], False)
+    stages['istft_engine'] = model.istft._pick_engine('ConviSTFT', model.istft.window, True)
     line = {'metric': MODEL['metric'], 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32 (bf16x3 split operands, fp32 accumulate)',

@@ -481,12 +481,13 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
               hi[j] = hb;
               lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
             }
-            uint4* dh = reinterpret_cast<uint4*>(cb + c0);
-            uint4* dl = reinterpret_cast<uint4*>(cb + lo_off + c0);
+            // 256-bit stores: a full 32-byte sector per lane and instruction (lanes are a pixel >= 128 B apart)
+            __nv_bfloat16* dh = cb + c0;
+            __nv_bfloat16* dl = cb + lo_off + c0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-              dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+            for (int j = 0; j < 2; ++j) {
+              ptx::st_global_v8(dh + 16 * j, hi + 8 * j);
+              ptx::st_global_v8(dl + 16 * j, lo + 8 * j);
             }
           }
         }

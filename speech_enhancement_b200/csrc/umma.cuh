@@ -208,5 +208,12 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16_f32(int M, int N) {
          (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// 256-bit global store (sm_100: STG.E.256): `ptr` 32-byte aligned
+__device__ __forceinline__ void st_global_v8(void* ptr, const uint32_t* v) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+               "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
 }  // namespace ptx
 }  // namespace se
