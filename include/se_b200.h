@@ -222,6 +222,15 @@ SE_API int se_ccbam_spatial_pool(const void* x_cl2, const float* ca, int64_t B, 
                                  void* stream);
 SE_API int se_ccbam_apply(const void* x_cl2, const float* ca, const float* sa, int64_t B, int64_t P, int C, int Cp,
                           void* y_cl2, void* stream);
+/*   se_ccbam_channel_attn   ca [B][C] = sigmoid(fc(mean) + fc(max)) from the partial statistics, fc(v) = w2 relu(w1 v)
+ *                           with dense real matrices w1 [R2][C], w2 [C][R2] (the shared complex MLP of ccbam.py:39-42;
+ *                           the reference's ComplexLinear is block diagonal, complex_nn.py:106-113)        (ccbam.py:45-63)
+ *   se_ccbam_spatial_attn   sa [B][2][H*W] = sigmoid(relu(bias + 7x7 conv of pooled, zero padding 3)); packed [2][4*49],
+ *                           bias [2] = the complex conv with its eval-mode complex BN folded in            (ccbam.py:65-86) */
+SE_API int se_ccbam_channel_attn(const float* partial, int nblk, int64_t P, const float* w1, const float* w2, int64_t B,
+                                 int C, int Cp, int R2, float* ca, void* stream);
+SE_API int se_ccbam_spatial_attn(const float* pooled, const float* packed, const float* bias, int64_t B, int H, int W,
+                                 float* sa, void* stream);
 
 /* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
  * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),

@@ -56,6 +56,8 @@ _SIGS = {
     'se_ccbam_channel_stats': (C.c_int, [_P, _L, _L, _I, _I, _P, _P]),
     'se_ccbam_spatial_pool': (C.c_int, [_P, _P, _L, _L, _I, _I, _P, _P]),
     'se_ccbam_apply': (C.c_int, [_P, _P, _P, _L, _L, _I, _I, _P, _P]),
+    'se_ccbam_channel_attn': (C.c_int, [_P, _I, _L, _P, _P, _L, _I, _I, _I, _P, _P]),
+    'se_ccbam_spatial_attn': (C.c_int, [_P, _P, _P, _L, _I, _I, _P, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_mask_bwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P, _P, _P, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),

@@ -369,27 +369,59 @@ class CCBAM(nn.Module):
         self.channel_attention_branch = _ChannelAttention(feature_map_channels, reduction)
         self.spatial_attention_branch = _SpatialAttention(ops)
 
+    def _attn_operands(self, dev):
+        """dense matrices of the shared MLP (the reference's ComplexLinear is block diagonal over the real / imaginary
+        halves, complex_nn.py:106-113) and the 7x7 attention conv with its eval-mode complex BN folded in; rebuilt when
+        a parameter or running statistic changes"""
+        from .chain import FusedBlock
+        fc = self.channel_attention_branch.shared_fc_layer
+        conv = self.spatial_attention_branch.conv
+        blk = self.__dict__.get('_sa_block')
+        if blk is None:
+            blk = self.__dict__['_sa_block'] = FusedBlock(conv.conv, conv.norm, conv.act)
+        ops = blk._operands()
+        lins = [fc[0].linear.real_linear, fc[0].linear.imag_linear, fc[1].linear.real_linear, fc[1].linear.imag_linear]
+        key = tuple((l.weight.data_ptr(), l.weight._version) for l in lins) + (id(ops['packed']),)
+        c = self.__dict__.get('_attn_ops')
+        if c is None or c[0] != key:
+            with torch.no_grad():
+                w1 = torch.block_diag(lins[0].weight.float(), lins[1].weight.float()).contiguous().to(dev)
+                w2 = torch.block_diag(lins[2].weight.float(), lins[3].weight.float()).contiguous().to(dev)
+            c = self.__dict__['_attn_ops'] = (key, w1, w2)
+        if ops['slope'] != 0.0 or ops['packed'].shape != (2, 4 * 49):
+            raise RuntimeError('CCBAM.forward_cl2: the spatial attention block must be a 7x7 complex conv 4 -> 2 + ReLU')
+        return c[1], c[2], ops['packed'], ops['bias']
+
     def forward_cl2(self, act):
-        """the same attention on a CL2 activation (chain.Act) in three passes of csrc/ccbam.cu; the shared
-        MLP, the 7x7 attention convolution and the sigmoids run on their tiny tensors as usual."""
+        """the same attention on a CL2 activation (chain.Act): five launches of csrc/ccbam.cu -- channel statistics,
+        channel attention (partial reduce + shared MLP + sigmoid), spatial pooling of x * ca, spatial attention
+        (7x7 conv + folded BN + ReLU + sigmoid), apply."""
         from . import _abi
         from .chain import Act
         x = act.data
         B, _, H, W, Cp = x.shape
         if (H, W) != (act.H, act.W):
             raise RuntimeError('CCBAM.forward_cl2: trimmed activations are not supported')
+        if self.training:
+            raise RuntimeError('CCBAM.forward_cl2: eval mode only (the complex BN of the attention conv is folded)')
         C, P = act.C, H * W
         lib = _abi.lib()
+        w1, w2, packed, bias = self._attn_operands(x.device)
+        if w1.shape[1] != C or w2.shape[0] != C:
+            raise RuntimeError(f'CCBAM.forward_cl2: attention MLP is built for {w1.shape[1]} channels, got {C}')
         with torch.cuda.device(x.device), _abi.stage('ccbam'):
             nb = lib.se_ccbam_num_partials(P)
             partial = torch.empty((B, nb, 2, Cp), device=x.device, dtype=torch.float32)
             _abi.check(lib.se_ccbam_channel_stats(_abi.ptr(x), B, P, C, Cp, _abi.ptr(partial), _abi.stream_ptr()))
-            fc = self.channel_attention_branch.shared_fc_layer
-            ca = torch.sigmoid(fc(partial[:, :, 0, :C].sum(1) / P) + fc(partial[:, :, 1, :C].amax(1))).contiguous()
+            ca = torch.empty((B, C), device=x.device, dtype=torch.float32)
+            _abi.check(lib.se_ccbam_channel_attn(_abi.ptr(partial), nb, P, _abi.ptr(w1), _abi.ptr(w2), B, C, Cp,
+                                                 w1.shape[0], _abi.ptr(ca), _abi.stream_ptr()))
             pooled = torch.empty((B, 4, H, W), device=x.device, dtype=torch.float32)
             _abi.check(lib.se_ccbam_spatial_pool(_abi.ptr(x), _abi.ptr(ca), B, P, C, Cp, _abi.ptr(pooled),
                                                  _abi.stream_ptr()))
-            sa = torch.sigmoid(self.spatial_attention_branch.conv(pooled)).contiguous()
+            sa = torch.empty((B, 2, H, W), device=x.device, dtype=torch.float32)
+            _abi.check(lib.se_ccbam_spatial_attn(_abi.ptr(pooled), _abi.ptr(packed), _abi.ptr(bias), B, H, W,
+                                                 _abi.ptr(sa), _abi.stream_ptr()))
             out = torch.empty_like(x)
             _abi.check(lib.se_ccbam_apply(_abi.ptr(x), _abi.ptr(ca), _abi.ptr(sa), B, P, C, Cp, _abi.ptr(out),
                                           _abi.stream_ptr()))

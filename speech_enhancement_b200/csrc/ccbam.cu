@@ -131,6 +131,82 @@ ccbam_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
   }
 }
 
+// channel attention map from the partial statistics (ccbam.py:45-63): mean / max descriptors -> shared MLP
+// (w1 [R2][C], ReLU, w2 [C][R2]; dense real matrices -- the reference's ComplexLinear is block diagonal over the real
+// and imaginary halves, complex_nn.py:106-113) on both -> sigmoid of the sum.  One block per batch row.
+__global__ void __launch_bounds__(128)
+ccbam_channel_attn_kernel(const float* __restrict__ partial, int nblk, float inv_p, const float* __restrict__ w1,
+                          const float* __restrict__ w2, int C, int Cp, int R2, float* __restrict__ ca) {
+  __shared__ float v[2][128], hdn[2][64];
+  const int64_t b = blockIdx.x;
+  const int c = threadIdx.x;
+  if (c < C) {
+    float a = 0.f, m = -FLT_MAX;
+    for (int k = 0; k < nblk; ++k) {
+      const float* pp = partial + ((b * nblk + k) * 2) * Cp + c;
+      a += pp[0];
+      m = fmaxf(m, pp[Cp]);
+    }
+    v[0][c] = a * inv_p;
+    v[1][c] = m;
+  }
+  __syncthreads();
+  if (c < 2 * R2) {
+    const int which = c / R2, j = c - which * R2;
+    float a = 0.f;
+    for (int k = 0; k < C; ++k) a = fmaf(__ldg(w1 + j * C + k), v[which][k], a);
+    hdn[which][j] = fmaxf(a, 0.f);
+  }
+  __syncthreads();
+  if (c < C) {
+    float a = 0.f, m = 0.f;
+    for (int j = 0; j < R2; ++j) {
+      const float w = __ldg(w2 + c * R2 + j);
+      a = fmaf(w, hdn[0][j], a);
+      m = fmaf(w, hdn[1][j], m);
+    }
+    ca[b * C + c] = 1.f / (1.f + expf(-(a + m)));
+  }
+}
+
+// spatial attention map (ccbam.py:65-86): 7x7 conv over the four pooled maps (zero padding 3) with the complex
+// conv + eval-mode complex BN folded into `packed` [2][4*49] / `bias` [2], ReLU, sigmoid.  32 x 8 output pixels per
+// block, the 14 x 38 x 4 input tile and the weights in shared memory.
+__global__ void __launch_bounds__(256)
+ccbam_spatial_attn_kernel(const float* __restrict__ pooled, const float* __restrict__ packed, const float* __restrict__ bias,
+                          int H, int W, float* __restrict__ sa) {
+  constexpr int TW = 32, TH = 8, R = 3, SW = TW + 2 * R, SH = TH + 2 * R;
+  __shared__ float tile[4][SH][SW + 1];
+  __shared__ float2 wts[4 * 49];
+  const int64_t b = blockIdx.z, P = (int64_t)H * W;
+  const int w0 = blockIdx.x * TW, h0 = blockIdx.y * TH;
+  for (int i = threadIdx.x; i < 4 * 49; i += 256) wts[i] = make_float2(__ldg(packed + i), __ldg(packed + 4 * 49 + i));
+  for (int i = threadIdx.x; i < 4 * SH * SW; i += 256) {
+    const int ch = i / (SH * SW), r = (i / SW) % SH, col = i % SW;
+    const int h = h0 + r - R, w = w0 + col - R;
+    tile[ch][r][col] = (h >= 0 && h < H && w >= 0 && w < W) ? __ldg(pooled + (b * 4 + ch) * P + (int64_t)h * W + w) : 0.f;
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int h = h0 + ty, w = w0 + tx;
+  float a0 = __ldg(bias), a1 = __ldg(bias + 1);
+#pragma unroll
+  for (int ch = 0; ch < 4; ++ch)
+#pragma unroll
+    for (int dh = 0; dh < 7; ++dh)
+#pragma unroll
+      for (int dw = 0; dw < 7; ++dw) {
+        const float x = tile[ch][ty + dh][tx + dw];
+        const float2 wv = wts[(ch * 7 + dh) * 7 + dw];
+        a0 = fmaf(wv.x, x, a0);
+        a1 = fmaf(wv.y, x, a1);
+      }
+  if (h < H && w < W) {
+    sa[(b * 2 + 0) * P + (int64_t)h * W + w] = 1.f / (1.f + expf(-fmaxf(a0, 0.f)));
+    sa[(b * 2 + 1) * P + (int64_t)h * W + w] = 1.f / (1.f + expf(-fmaxf(a1, 0.f)));
+  }
+}
+
 }  // namespace se
 
 static int ccbam_check(const char* nm, int64_t B, int64_t P, int C, int Cp) {
@@ -172,4 +248,25 @@ extern "C" int se_ccbam_apply(const void* x_cl2, const float* ca, const float* s
   se::ccbam_apply_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const __nv_bfloat16*>(x_cl2), ca, sa, P, C, Cp,
                                                                  reinterpret_cast<__nv_bfloat16*>(y_cl2));
   return se::check_launch("se_ccbam_apply");
+}
+
+extern "C" int se_ccbam_channel_attn(const float* partial, int nblk, int64_t P, const float* w1, const float* w2, int64_t B,
+                                     int C, int Cp, int R2, float* ca, void* stream) {
+  SE_REQUIRE(partial && w1 && w2 && ca, "se_ccbam_channel_attn: null pointer");
+  int rc = ccbam_check("se_ccbam_channel_attn", B, P, C, Cp);
+  if (rc != SE_OK || B == 0) return rc;
+  if (nblk <= 0 || R2 <= 0 || R2 > 64) return se::fail(SE_ERR_UNSUPPORTED, "se_ccbam_channel_attn: needs 0 < R2 <= 64");
+  se::ccbam_channel_attn_kernel<<<(unsigned)B, 128, 0, (cudaStream_t)stream>>>(partial, nblk, 1.0f / (float)P, w1, w2, C, Cp,
+                                                                               R2, ca);
+  return se::check_launch("se_ccbam_channel_attn");
+}
+
+extern "C" int se_ccbam_spatial_attn(const float* pooled, const float* packed, const float* bias, int64_t B, int H, int W,
+                                     float* sa, void* stream) {
+  SE_REQUIRE(pooled && packed && bias && sa, "se_ccbam_spatial_attn: null pointer");
+  SE_REQUIRE(B >= 0 && H > 0 && W > 0 && B <= 65535 && (H + 7) / 8 <= 65535, "se_ccbam_spatial_attn: bad dims");
+  if (B == 0) return SE_OK;
+  dim3 grid((unsigned)((W + 31) / 32), (unsigned)((H + 7) / 8), (unsigned)B);
+  se::ccbam_spatial_attn_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(pooled, packed, bias, H, W, sa);
+  return se::check_launch("se_ccbam_spatial_attn");
 }

@@ -429,6 +429,29 @@ def test_dcunet_frcrn_fused_chain_matches_modular_path_and_oracle(cls, args, L):
         agree(spec_m, wav_m, spec_ref, wav_ref, 3e-4)
 
 
+@pytest.mark.parametrize('B,C,H,W', [(2, 128, 37, 53), (3, 64, 9, 70), (1, 32, 5, 3)])
+def test_ccbam_on_cl2_matches_the_module_path(B, C, H, W):
+    """csrc/ccbam.cu (statistics, channel attention MLP, spatial pooling, 7x7 attention conv with folded BN, apply)
+    against the module's own NCHW forward (ccbam.py:28-106) and the CPU oracle modules"""
+    from speech_enhancement_b200 import chain
+    m = callers.CCBAM(C, 16).eval()
+    sd = seeded_state_dict(m, seed=12)
+    m.load_state_dict(sd)
+    ref = callers.CCBAM(C, 16, ops=OPS).eval()
+    ref.load_state_dict(sd)
+    x = rand((B, C, H, W), 77, 1.0)
+    with torch.no_grad():
+        want = ref(x)
+        m.to(DEV)
+        y_mod = m(x.to(DEV))
+        m.forward_cl2(chain.cl2_from_nchw(x.to(DEV)))           # builds the cached folded operands
+        n0 = _abi.lib().se_launch_count()
+        y = chain.cl2_to_nchw(m.forward_cl2(chain.cl2_from_nchw(x.to(DEV))))
+        assert _abi.lib().se_launch_count() - n0 == 7            # 2 layout conversions + the 5 attention kernels
+    assert rel_l2(y_mod.cpu(), want) < TOL_EXACT
+    assert rel_l2(y.cpu(), want) < 2e-5                          # CL2 carries ~16 mantissa bits
+
+
 def test_cl2_roundtrip_and_two_source_block():
     from speech_enhancement_b200 import chain
     x = rand((2, 40, 9, 37), 3).to(DEV)
