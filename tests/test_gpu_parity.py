@@ -452,6 +452,26 @@ def test_ccbam_on_cl2_matches_the_module_path(B, C, H, W):
     assert rel_l2(y.cpu(), want) < 2e-5                          # CL2 carries ~16 mantissa bits
 
 
+def test_host_pipeline_overlapped_copies_give_the_same_waveforms():
+    """HostPipeline (H2D / forward / D2H of neighbouring batches on three streams) == model(x)[1], batch by batch"""
+    from speech_enhancement_b200.pipeline import HostPipeline
+    m = callers.DCCRN('dccrn-CL', 400, 100, 512).eval()
+    m.load_state_dict(seeded_state_dict(m, seed=3))
+    m.to(DEV)
+    xs = [synth_noisy_speech(3, 12000, seed=40 + i).pin_memory() for i in range(5)]
+    pipe = HostPipeline(m)
+    n = pipe.output_length(xs[0])
+    outs = [torch.empty((3, n)).pin_memory() for _ in xs]
+    for x, o in zip(xs, outs):
+        pipe.submit(x, o)
+    pipe.synchronize()
+    with torch.no_grad():
+        for x, o in zip(xs, outs):
+            assert torch.equal(o, m(x.to(DEV))[1].cpu())
+    with pytest.raises(RuntimeError):
+        pipe.submit(torch.zeros(3, 12000), outs[0])               # not pinned
+
+
 def test_cl2_roundtrip_and_two_source_block():
     from speech_enhancement_b200 import chain
     x = rand((2, 40, 9, 37), 3).to(DEV)
