@@ -18,6 +18,7 @@
 // shared memory so that every global access is a contiguous run along the frame axis.
 #include <utility>
 #include "common.cuh"
+#include "umma.cuh"
 
 namespace se {
 namespace {
@@ -156,10 +157,6 @@ __device__ __forceinline__ void cp_async8(float* smem_dst, const float* gsrc, bo
   int sz = valid ? 8 : 0;
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
 }
-__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
-  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
-}
 // warp index as a warp-uniform value: lets the compiler keep the per-pair loops (and the shuffles inside) convergent
 __device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
@@ -178,10 +175,19 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
   const int tid = threadIdx.x, lane = tid & 31, warp = uniform_warp_idx();
   constexpr int F = NFFT / 2 + 1;
 
-  // stage a tile's samples once (each is used by ceil(win / hop) frames), mirroring at the clip ends
-  // (F.pad(mode='reflect'), conv_stft.py:55); the NFFT - win floats behind the last frame are zeroed so that the
-  // frame loads below need no bounds predicate (they are multiplied by a zero window tap)
-  auto stage = [&](int idx, float* dst) {
+  // stage a tile's samples once (each is used by ceil(win / hop) frames).  Interior tiles whose first sample is
+  // 16-byte aligned are ONE TMA bulk copy (cp.async.bulk -> mbarrier) issued by a single thread; tiles that touch the
+  // clip ends mirror sample by sample (F.pad(mode='reflect'), conv_stft.py:55) with 4-byte cp.async.  The NFFT - win
+  // floats behind the last frame are zeroed so that the frame loads below need no bounds predicate (they are
+  // multiplied by a zero window tap).
+  __shared__ __align__(8) uint64_t bars[2];
+  if (tid == 0) {
+    ptx::mbar_init(&bars[0], 1);
+    ptx::mbar_init(&bars[1], 1);
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  auto stage = [&](int idx, float* dst, uint64_t* bar) {
     const int b = idx / tiles, t0 = (idx - b * tiles) * TILE;
     const int nfr = min(TILE, T - t0);
     const int nsamp = (nfr - 1) * hop + win;
@@ -189,9 +195,13 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
     const float* xb = x + (int64_t)b * L;
     if (s0 >= 0 && s0 + nsamp <= L && ((reinterpret_cast<uintptr_t>(xb + s0) & 15) == 0)) {
       const float* src = xb + s0;
-      const int n4 = nsamp >> 2;
-      for (int i = tid; i < n4; i += THREADS) cp_async16(dst + 4 * i, src + 4 * i);
-      if (tid < (nsamp & 3)) cp_async4(dst + 4 * n4 + tid, src + 4 * n4 + tid);
+      const int n4 = nsamp & ~3;
+      if (tid == 0) {
+        ptx::fence_proxy_async_smem();         // the buffer was read through the generic proxy one tile ago
+        ptx::mbar_arrive_expect_tx(bar, (uint32_t)n4 * 4u);
+        ptx::tma_bulk_load_1d(dst, src, (uint32_t)n4 * 4u, bar);
+      }
+      if (tid < nsamp - n4) cp_async4(dst + n4 + tid, src + n4 + tid);
     } else {
       for (int i = tid; i < nsamp; i += THREADS) {
         int64_t sidx = s0 + i;
@@ -199,13 +209,14 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
         else if (sidx >= L) sidx = 2 * (L - 1) - sidx;
         cp_async4(dst + i, xb + sidx);
       }
+      if (tid == 0) ptx::mbar_arrive(bar);
     }
     for (int i = tid; i < NFFT - win; i += THREADS) dst[nsamp + i] = 0.0f;
     cp_async_commit();
   };
 
   int idx = blockIdx.x;
-  if (idx < total) stage(idx, xs);
+  if (idx < total) stage(idx, xs, &bars[0]);
   float2 tw[16];
   lane_twiddles(tw, lane);
   float wl[16];                              // window taps of this lane, times the 1/2 of the pair separation
@@ -216,13 +227,14 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
   });
   const bool t_even = (T & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0;
 
-  for (int buf = 0; idx < total; idx += gridDim.x, buf ^= 1) {
+  for (int buf = 0, it = 0; idx < total; idx += gridDim.x, buf ^= 1, ++it) {
     const int b = idx / tiles, t0 = (idx - b * tiles) * TILE;
     const int nfr = min(TILE, T - t0);
     const float* xc = xs + buf * xs_cap;
+    ptx::mbar_wait(&bars[buf], (uint32_t)(it >> 1) & 1u);
     cp_async_wait_all();
     __syncthreads();                         // this tile's samples landed; everyone left the previous write-out
-    if (idx + (int)gridDim.x < total) stage(idx + gridDim.x, xs + (buf ^ 1) * xs_cap);
+    if (idx + (int)gridDim.x < total) stage(idx + gridDim.x, xs + (buf ^ 1) * xs_cap, &bars[buf ^ 1]);
 
     const int npairs = (nfr + 1) >> 1;
     for (int p = warp; p < npairs; p += WARPS) {
