@@ -30,6 +30,8 @@ constexpr int WARPS = THREADS / 32;
 constexpr int ZPITCH = 529;     // float2 per pair row: >= 16*33 transpose scratch, odd -> conflict-free columns
 constexpr int TPITCH = 33;      // transpose scratch row pitch (float2)
 constexpr int MAXJ = 8;         // ceil(win / hop) covered by the inverse kernel
+constexpr int FTHREADS = 512;   // forward kernel: 16 warps = the 16 frame pairs of a tile
+constexpr int FWARPS = FTHREADS / 32;
 
 template <int... I, class F>
 __device__ __forceinline__ void static_for_impl(std::integer_sequence<int, I...>, F&& f) {
@@ -136,6 +138,43 @@ __device__ __forceinline__ void warp_fft512(float2 (&v)[16], const float2 (&tw)[
     constexpr int k = decltype(k_)::value; v[k] = r[k]; });
 }
 
+// Same transform with the stage twiddles read from a shared-memory table tw_s[k2 * 32 + lane] (built once per CTA)
+// and the results handed to `emit(k, Z[16 k + 256 h + k2])` instead of staying in registers: 64 registers per thread
+// instead of 128, i.e. 32 resident warps per SM instead of 16.
+template <bool INV, class Emit>
+__device__ __forceinline__ void warp_fft512_emit(float2 (&v)[16], const float2* __restrict__ tw_s, float2* row, int lane,
+                                                 Emit&& emit) {
+  fft16<INV>(v);
+  static_for<16>([&](auto k2_) {
+    constexpr int k2 = decltype(k2_)::value;
+    float2 y = v[brev4(k2)];
+    if constexpr (k2 != 0) {
+      const float2 t = tw_s[k2 * 32 + lane];
+      y = cmul_w<INV>(y, t.x, t.y);
+    }
+    row[k2 * TPITCH + lane] = y;
+  });
+  __syncwarp();
+  const int h = lane >> 4, k2l = lane & 15;
+  static_for<16>([&](auto m_) {
+    constexpr int m = decltype(m_)::value;
+    v[m] = row[k2l * TPITCH + 2 * m + h];
+  });
+  __syncwarp();
+  fft16<INV>(v);
+  const float sgn = h ? -1.0f : 1.0f;
+  static_for<16>([&](auto k_) {
+    constexpr int k = decltype(k_)::value;
+    float2 mine = v[brev4(k)];
+    if constexpr (k != 0) {                  // odd half: times W32^k before the last butterfly
+      float c = h ? cos32(k) : 1.0f, sn = h ? sin32(k) : 0.0f;
+      mine = cmul_w<INV>(mine, c, sn);
+    }
+    float2 other = make_float2(__shfl_xor_sync(0xffffffffu, mine.x, 16), __shfl_xor_sync(0xffffffffu, mine.y, 16));
+    emit(k_, make_float2(fmaf(sgn, mine.x, other.x), fmaf(sgn, mine.y, other.y)));   // E + O' (h = 0) / E - O' (h = 1)
+  });
+}
+
 __device__ __forceinline__ void lane_twiddles(float2 (&tw)[16], int lane) {
   static_for<16>([&](auto k2_) {
     constexpr int k2 = decltype(k2_)::value;
@@ -166,12 +205,14 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // out[b, f, t] = Re X_t[f], out[b, F + f, t] = Im X_t[f],  X_t = rfft_N( window * reflect_pad(x)[t*hop : t*hop + win] )
 // Persistent CTAs walk the (utterance, tile of 32 frames) list; the next tile's samples stream into the other half of
 // a double buffer while this tile is transformed.
-__global__ void __launch_bounds__(THREADS, 2)
+__global__ void __launch_bounds__(FTHREADS, 2)
 stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict__ window, int win, int hop, int pad,
                 float* __restrict__ out, int T, int tiles, int total, int xs_cap) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* zbuf = reinterpret_cast<float2*>(smem_raw);                   // [TILE/2][ZPITCH]
-  float* xs = reinterpret_cast<float*>(zbuf + (TILE / 2) * ZPITCH);     // [2][xs_cap] staged samples
+  float2* tw_s = zbuf + (TILE / 2) * ZPITCH;                            // [16][32] stage twiddles exp(-2 pi i lane k2 / 512)
+  float* wl_s = reinterpret_cast<float*>(tw_s + 16 * 32);               // [NFFT] window / 2 (0 beyond win)
+  float* xs = wl_s + NFFT;                                              // [2][xs_cap] staged samples
   const int tid = threadIdx.x, lane = tid & 31, warp = uniform_warp_idx();
   constexpr int F = NFFT / 2 + 1;
 
@@ -203,7 +244,7 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
       }
       if (tid < nsamp - n4) cp_async4(dst + n4 + tid, src + n4 + tid);
     } else {
-      for (int i = tid; i < nsamp; i += THREADS) {
+      for (int i = tid; i < nsamp; i += FTHREADS) {
         int64_t sidx = s0 + i;
         if (sidx < 0) sidx = -sidx;
         else if (sidx >= L) sidx = 2 * (L - 1) - sidx;
@@ -211,20 +252,19 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
       }
       if (tid == 0) ptx::mbar_arrive(bar);
     }
-    for (int i = tid; i < NFFT - win; i += THREADS) dst[nsamp + i] = 0.0f;
+    for (int i = tid; i < NFFT - win; i += FTHREADS) dst[nsamp + i] = 0.0f;
     cp_async_commit();
   };
 
   int idx = blockIdx.x;
   if (idx < total) stage(idx, xs, &bars[0]);
-  float2 tw[16];
-  lane_twiddles(tw, lane);
-  float wl[16];                              // window taps of this lane, times the 1/2 of the pair separation
-  static_for<16>([&](auto n2_) {
-    constexpr int n2 = decltype(n2_)::value;
-    int n = lane + 32 * n2;
-    wl[n2] = n < win ? 0.5f * __ldg(window + n) : 0.0f;
-  });
+  for (int i = tid; i < 16 * 32; i += FTHREADS) {
+    float sn, cs;
+    sincospif((float)((i >> 5) * (i & 31)) * (1.0f / 256.0f), &sn, &cs);      // angle 2 pi lane k2 / 512
+    tw_s[i] = make_float2(cs, sn);
+  }
+  // window taps times the 1/2 of the pair separation
+  for (int i = tid; i < NFFT; i += FTHREADS) wl_s[i] = i < win ? 0.5f * __ldg(window + i) : 0.0f;
   const bool t_even = (T & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0;
 
   for (int buf = 0, it = 0; idx < total; idx += gridDim.x, buf ^= 1, ++it) {
@@ -237,22 +277,22 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
     if (idx + (int)gridDim.x < total) stage(idx + gridDim.x, xs + (buf ^ 1) * xs_cap, &bars[buf ^ 1]);
 
     const int npairs = (nfr + 1) >> 1;
-    for (int p = warp; p < npairs; p += WARPS) {
+    if (warp < npairs) {                     // one pair of frames per warp
+      const int p = warp;
       const float* fa = xc + (2 * p) * hop + lane;
       const bool has_b = 2 * p + 1 < nfr;
       const float* fb = has_b ? fa + hop : fa;
       float2 v[16];
       static_for<16>([&](auto n2_) {
         constexpr int n2 = decltype(n2_)::value;
-        v[n2] = make_float2(fa[32 * n2] * wl[n2], fb[32 * n2] * wl[n2]);
+        const float w = wl_s[lane + 32 * n2];
+        v[n2] = make_float2(fa[32 * n2] * w, has_b ? fb[32 * n2] * w : 0.0f);
       });
-      if (!has_b) static_for<16>([&](auto n2_) { v[decltype(n2_)::value].y = 0.0f; });
       float2* row = zbuf + p * ZPITCH;
-      warp_fft512<false>(v, tw, row, lane);
-      const int h = lane >> 4, k2 = lane & 15;
-      static_for<16>([&](auto k_) {
+      const int base = 256 * (lane >> 4) + (lane & 15);
+      warp_fft512_emit<false>(v, tw_s, row, lane, [&](auto k_, float2 z) {
         constexpr int k = decltype(k_)::value;
-        row[16 * k + 256 * h + k2] = v[k];
+        row[16 * k + base] = z;
       });
     }
     __syncthreads();
@@ -266,17 +306,17 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
       const bool has_b = 2 * p + 1 < nfr;
       const float2* zr = zbuf + p * ZPITCH;
       float* pre = out + (int64_t)b * (2 * F) * T + (t0 + 2 * p) + (int64_t)(2 * warp + fo) * T;
-      const int64_t im_off = (int64_t)F * T, step = (int64_t)(2 * WARPS) * T;
+      const int64_t im_off = (int64_t)F * T, step = (int64_t)(2 * FWARPS) * T;
       if (t_even && has_b) {
 #pragma unroll 4
-        for (int f = 2 * warp + fo; f < F; f += 2 * WARPS, pre += step) {
+        for (int f = 2 * warp + fo; f < F; f += 2 * FWARPS, pre += step) {
           float2 z1 = zr[f], z2 = zr[(NFFT - f) & (NFFT - 1)];
           *reinterpret_cast<float2*>(pre) = make_float2(z1.x + z2.x, z1.y + z2.y);
           *reinterpret_cast<float2*>(pre + im_off) = make_float2(z1.y - z2.y, z2.x - z1.x);
         }
       } else {
 #pragma unroll 2
-        for (int f = 2 * warp + fo; f < F; f += 2 * WARPS, pre += step) {
+        for (int f = 2 * warp + fo; f < F; f += 2 * FWARPS, pre += step) {
           float2 z1 = zr[f], z2 = zr[(NFFT - f) & (NFFT - 1)];
           pre[0] = z1.x + z2.x;
           pre[im_off] = z1.y - z2.y;
@@ -460,7 +500,8 @@ extern "C" int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float
   int64_t tiles = (T + TILE - 1) / TILE;
   SE_REQUIRE(T < (1 << 30) && tiles * B < (1ll << 31), "se_stft_fft_fwd: batch x frame count too large");
   int xs_cap = ((TILE - 1) * hop + NFFT + 3) & ~3;
-  size_t smem = (size_t)(TILE / 2) * ZPITCH * sizeof(float2) + 2 * (size_t)xs_cap * sizeof(float);
+  size_t smem = (size_t)(TILE / 2) * ZPITCH * sizeof(float2) + 16 * 32 * sizeof(float2) + NFFT * sizeof(float) +
+                2 * (size_t)xs_cap * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
     SE_CUDA(cudaFuncSetAttribute(stft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024));
@@ -468,7 +509,7 @@ extern "C" int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float
   }
   int total = (int)(tiles * B);
   int grid = total < 2 * num_sms() ? total : 2 * num_sms();
-  stft_fft_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(x, L, window, win, hop, pad, out, (int)T, (int)tiles,
+  stft_fft_kernel<<<grid, FTHREADS, smem, (cudaStream_t)stream>>>(x, L, window, win, hop, pad, out, (int)T, (int)tiles,
                                                                  total, xs_cap);
   return check_launch("se_stft_fft_fwd");
 }
