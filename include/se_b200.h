@@ -171,6 +171,11 @@ SE_API int se_cl2_from_rows(const float* x, int64_t M, int K, int64_t ld, void* 
 SE_API int se_stft_frames_cl2(const float* x, int64_t B, int64_t L, int hop, int pad, int Q, int Cp, void* cl2,
                        void* stream);
 SE_API int se_cl2_to_nchw(const void* cl2, int64_t B, int C, int H, int W, int Cp, float* y, void* stream);
+/* rows [B*T][ld] fp32, column part*(C/2)*F + c*F + f = channel part*C/2 + c at frequency row f (the [B, T, C*F] output
+ * of the LSTM block, _2008_00264_dccrn.py:161-165) -> CL2 [B][2][F][T][Cp]: the reference's permute + reshape back to
+ * [B, C, F, T] fused with the layout conversion.                                                                   */
+SE_API int se_cl2_from_lstm_rows(const float* rows, int64_t ld, int64_t B, int C, int F, int T, void* cl2, int Cp,
+                                 void* stream);
 SE_API int64_t se_cconv_wq_elems(int Cout2, int Cp_total, int taps);
 SE_API int se_cconv_prep_weight(const float* packed, int Cout2, int Cin2, int taps, const int* chan_map,
                                 int Cp_total, void* wq, void* stream);

@@ -37,6 +37,7 @@ _SIGS = {
     'se_cl2_from_strided': (C.c_int, [_P, _L, _L, _L, _L, _I, _I, _I, _P, _I, _P]),
     'se_stft_frames_cl2': (C.c_int, [_P, _L, _L, _I, _I, _I, _I, _P, _P]),
     'se_cl2_to_nchw': (C.c_int, [_P, _L, _I, _I, _I, _I, _P, _P]),
+    'se_cl2_from_lstm_rows': (C.c_int, [_P, _L, _L, _I, _I, _I, _P, _I, _P]),
     'se_cconv_wq_elems': (C.c_int64, [_I, _I, _I]),
     'se_cconv_prep_weight': (C.c_int, [_P, _I, _I, _I, _P, _I, _P, _P]),
     'se_cconv_gemm': (C.c_int, [_P, _P]),

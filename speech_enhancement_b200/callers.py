@@ -141,7 +141,7 @@ class DCCRN(nn.Module):
         return self._fb
 
     def _forward_fused(self, x):
-        from .chain import cl2_from_nchw
+        from .chain import cl2_from_lstm_rows
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)                                               # [B, 2F, T] fp32
         B, C2, T = spec.shape
@@ -150,14 +150,19 @@ class DCCRN(nn.Module):
         # enc0 reads the real / imag row blocks of `spec` in place (DC bin skipped, causal frame pad)
         act, _ = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1)
         skips = [act]
-        nchw = None
+        rows = None
         for i in range(1, len(enc)):
-            last = i == len(enc) - 1
-            act, nchw = enc[i]([act], pad_left=1, out_cl2=True, out_nchw=last)
+            if i == len(enc) - 1:
+                # the last encoder layer also writes its output as the [B, T, C*F] rows the LSTM block reads
+                # (dccrn.py:161-163: column c*F + f), next to the CL2 skip
+                c = enc[i].cout2
+                f, t = enc[i].out_size(act.H, act.W, 0, 1)
+                rows = torch.empty((B, t, c * f), device=spec.device, dtype=torch.float32)
+                act, _ = enc[i]([act], pad_left=1, out_cl2=True, y_out=rows, y_strides=(t * c * f, f, 1, c * f))
+            else:
+                act, _ = enc[i]([act], pad_left=1, out_cl2=True)
             skips.append(act)
-        b, c, f, t = nchw.shape
-        h = self.lstm(nchw.reshape(b, c * f, t).permute(0, 2, 1))
-        act = cl2_from_nchw(h.permute(0, 2, 1).reshape(b, c, f, t))
+        act = cl2_from_lstm_rows(self.lstm(rows), B, c, f, t)
         y = None
         for i, blk in enumerate(dec):
             skip = skips.pop()
@@ -491,20 +496,26 @@ class FRCRN(nn.Module):
         shift, complex_concat as a second source, the bottom-row F.pad by out-of-bounds fill), the CCBAM
         attention applied to the CL2 skips by csrc/ccbam.cu; the real final_conv reads the last decoder's CL2
         output as a RealConvBlock."""
-        from .chain import cl2_from_nchw
+        from .chain import cl2_from_lstm_rows
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)
         B, C2, T = spec.shape
         noisy_real, noisy_imag = _spec_planes(spec, n_bins)
         enc, dec = self._fused_blocks()
-        act, nchw = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1)
+        act, _ = enc[0].first_layer(spec[:, 1:], C2 * T, n_bins * T, T, B, n_bins - 1, T, pad_left=1)
         skips = [act]
+        rows = None
         for i in range(1, len(enc)):
-            act, nchw = enc[i]([act], pad_left=1, out_cl2=True, out_nchw=i == len(enc) - 1)
+            if i == len(enc) - 1:
+                # the last encoder layer also writes the [B, T, C*F] rows the LSTM reads (frcrn.py: column c*F + f)
+                c = enc[i].cout2
+                f, t = enc[i].out_size(act.H, act.W, 0, 1)
+                rows = torch.empty((B, t, c * f), device=spec.device, dtype=torch.float32)
+                act, _ = enc[i]([act], pad_left=1, out_cl2=True, y_out=rows, y_strides=(t * c * f, f, 1, c * f))
+            else:
+                act, _ = enc[i]([act], pad_left=1, out_cl2=True)
             skips.append(act)
-        b, c, f, t = nchw.shape
-        h = self.lstm(nchw.reshape(b, c * f, t).permute(0, 2, 1))
-        act = cl2_from_nchw(h.permute(0, 2, 1).reshape(b, c, f, t))
+        act = cl2_from_lstm_rows(self.lstm(rows), B, c, f, t)
         y = None
         n = len(dec)
         for i, (att, blk) in enumerate(zip(self.decoder.skip_connection_attention_layers, dec)):

@@ -62,6 +62,20 @@ def cl2_from_nchw(x):
     return out
 
 
+def cl2_from_lstm_rows(rows, B, C_, F_, T):
+    """[B, T, C*F] fp32 (the LSTM block's output, column part*(C/2)*F + c*F + f) -> CL2 Act [B, C, F, T]: the reference's
+    permute(0, 2, 1).reshape(B, C, F, T) (_2008_00264_dccrn.py:164-165) fused with the layout conversion"""
+    rows = _abi.require_cuda_f32(rows, 'cl2_from_lstm_rows(rows)')
+    if rows.dim() != 3 or rows.shape[0] != B or rows.shape[1] != T or rows.shape[2] != C_ * F_ or rows.stride(2) != 1 \
+            or rows.stride(0) != T * rows.stride(1):
+        raise RuntimeError(f'cl2_from_lstm_rows: expected [B={B}, T={T}, {C_ * F_}] rows, got {tuple(rows.shape)}')
+    out = cl2_empty(B, C_, F_, T, rows.device)
+    with torch.cuda.device(rows.device), _abi.stage('cl2'):
+        _abi.check(_abi.lib().se_cl2_from_lstm_rows(_abi.ptr(rows), rows.stride(1), B, C_, F_, T, _abi.ptr(out.data),
+                                                    out.Cp, _abi.stream_ptr()))
+    return out
+
+
 def cl2_to_nchw(act):
     d = act.data
     if d.shape[2] != act.H or d.shape[3] != act.W:
@@ -213,8 +227,11 @@ class FusedBlock:
         return ((H + pad_top + 2 * self.ph - self.kh) // self.sh + 1,
                 (W + pad_left + 2 * self.pw - self.kw) // self.sw + 1)
 
-    def __call__(self, srcs, pad_top=0, pad_left=0, out_cl2=True, out_nchw=False):
-        """srcs: list of Act with the same logical H, W.  Returns (Act | None, NCHW fp32 tensor | None)."""
+    def __call__(self, srcs, pad_top=0, pad_left=0, out_cl2=True, out_nchw=False, y_out=None, y_strides=None):
+        """srcs: list of Act with the same logical H, W.  Returns (Act | None, NCHW fp32 tensor | None).
+        `y_out` (fp32 CUDA tensor) + `y_strides` = (batch, channel, row, column) strides in elements: the fp32 copy of
+        the output is written there instead of a fresh NCHW tensor -- e.g. straight into the [B, T, C*F] rows the LSTM
+        block reads (_2008_00264_dccrn.py:161-163), with no permute / reshape copy in between."""
         ops = self._operands()
         if len(srcs) != len(self.src_channels) or any(s.C != c for s, c in zip(srcs, self.src_channels)):
             raise RuntimeError(f'FusedBlock: expected sources with channels {self.src_channels}')
@@ -226,6 +243,10 @@ class FusedBlock:
         dev = srcs[0].data.device
         y_act = cl2_empty(B, self.cout2, Ho, Wo, dev) if out_cl2 else None
         y = torch.empty((B, self.cout2, Ho, Wo), device=dev, dtype=torch.float32) if out_nchw else None
+        if y_out is not None:
+            if out_nchw or self.scatter_form or y_out.dtype != torch.float32 or not y_out.is_cuda or y_strides is None:
+                raise RuntimeError('FusedBlock: y_out needs y_strides, fp32 CUDA storage and out_nchw=False')
+            y = y_out
         a = _abi.ConvArgs()
         a.transposed, a.B, a.nsrc = int(self.transposed), B, len(srcs)
         for i, s in enumerate(srcs):
@@ -239,6 +260,8 @@ class FusedBlock:
         a.y_nchw = y.data_ptr() if y is not None else None
         a.y_cl2 = y_act.data.data_ptr() if y_act is not None else None
         a.y_Cp = y_act.Cp if y_act is not None else 0
+        if y_out is not None:
+            a.y_bs, a.y_cs, a.y_hs, a.y_ws = (int(v) for v in y_strides)
         if self.scatter_form and out_nchw and not out_cl2:
             ncol = self.kh * self.kw * self.cout2
             Np = (ncol + 3) // 4 * 4

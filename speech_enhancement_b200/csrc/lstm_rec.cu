@@ -10,6 +10,7 @@
 // column (4H = 512 threads for H = 128) keeps its W_hh row on chip for the whole sequence -- KR
 // values in registers, the other H-KR in shared memory, column-major so a warp reads consecutive
 // words -- and h_{t-1} is broadcast from shared memory.  Two __syncthreads per step.
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdlib>
@@ -318,4 +319,57 @@ extern "C" int se_lstm_rec_pair_fwd(const float* pre_gates, int64_t pre_ld, cons
   SE_REQUIRE(N >= 0 && T >= 0 && H > 0 && pre_ld >= 8 * (int64_t)H, "se_lstm_rec_pair_fwd: bad dims");
   if (N == 0 || T == 0) return SE_OK;
   return lstm_rec_any(pre_gates, pre_ld, w_hh0, w_hh1, h_out0, h_out1, 2, N, T, H, (cudaStream_t)stream);
+}
+
+// ---- LSTM-block output rows -> CL2 decoder input ---------------------------------------------------------------
+// The reference reshapes the [B, T, C*F] output of the LSTM block back to [B, C, F, T] (_2008_00264_dccrn.py:164-165,
+// column j = part * (C/2) * F + c * F + f for channel part * C/2 + c, complex halves first).  This kernel does that
+// permutation while converting to the engine's CL2 format [B][2][F][T][Cp] (bf16 hi | lo), one (b, t) row per block
+// staged through shared memory, 16-byte stores of 8 channels -- instead of a transposing copy + se_cl2_from_nchw.
+namespace se {
+__global__ void __launch_bounds__(128)
+cl2_from_lstm_rows_kernel(const float* __restrict__ rows, int64_t ld, int C, int F, int T, int Cp,
+                          __nv_bfloat16* __restrict__ out) {
+  extern __shared__ float row_s[];                 // [C * F]
+  const int64_t r = blockIdx.x;                    // row = b * T + t
+  const int64_t b = r / T;
+  const int t = (int)(r - b * T);
+  const int K = C * F, half = (C / 2) * F;
+  const float* src = rows + r * ld;
+  for (int i = threadIdx.x; i < K; i += blockDim.x) row_s[i] = __ldg(src + i);
+  __syncthreads();
+  const int groups = Cp / 8;
+  const int64_t plane = (int64_t)F * T * Cp;
+  for (int i = threadIdx.x; i < F * groups; i += blockDim.x) {
+    const int f = i / groups, c0 = (i - f * groups) * 8;
+    __align__(16) __nv_bfloat16 hi[8], lo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int ch = c0 + j;
+      float v = 0.f;
+      if (ch < C) {
+        const int part = ch >= C / 2, c = ch - part * (C / 2);
+        v = row_s[part * half + c * F + f];
+      }
+      hi[j] = __float2bfloat16_rn(v);
+      lo[j] = __float2bfloat16_rn(v - __bfloat162float(hi[j]));
+    }
+    __nv_bfloat16* dst = out + (b * 2) * plane + ((int64_t)f * T + t) * Cp + c0;
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(hi);
+    *reinterpret_cast<uint4*>(dst + plane) = *reinterpret_cast<const uint4*>(lo);
+  }
+}
+}  // namespace se
+
+extern "C" int se_cl2_from_lstm_rows(const float* rows, int64_t ld, int64_t B, int C, int F, int T, void* cl2, int Cp,
+                                     void* stream) {
+  SE_REQUIRE(rows && cl2, "se_cl2_from_lstm_rows: null pointer");
+  SE_REQUIRE(B >= 0 && C > 0 && C % 2 == 0 && F > 0 && T > 0 && Cp >= C && Cp % 64 == 0 && ld >= (int64_t)C * F,
+             "se_cl2_from_lstm_rows: bad dims");
+  if ((int64_t)C * F > 8192) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_lstm_rows: needs C * F <= 8192");
+  if (B * T > 0x7fffffffll) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_lstm_rows: too many rows");
+  if (B == 0) return SE_OK;
+  se::cl2_from_lstm_rows_kernel<<<(unsigned)(B * T), 128, (size_t)C * F * sizeof(float), (cudaStream_t)stream>>>(
+      rows, ld, C, F, T, Cp, reinterpret_cast<__nv_bfloat16*>(cl2));
+  return se::check_launch("se_cl2_from_lstm_rows");
 }

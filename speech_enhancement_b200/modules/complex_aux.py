@@ -43,25 +43,38 @@ def lstm_pair_forward(owner, lstms, x, engine):
     GEMM, each time loop runs in se_lstm_rec_fwd.  engine 'umma' puts the projections on the bf16x3
     tensor-core GEMM, 'torch' leaves them to fp32 F.linear."""
     from ..chain import LinearOperand
-    N, T, _ = x.shape
+    # `x` may be a list of row blocks [n_i, T, in] that are stacked on the batch axis WITHOUT a copy: views with a
+    # free row stride (the real / imaginary halves of a [B, T, 2*in] tensor) go through the projection one by one
+    parts = list(x) if isinstance(x, (list, tuple)) else [x]
+    T = parts[0].shape[1]
+    N = sum(p.shape[0] for p in parts)
+    dev = parts[0].device
     H, L = lstms[0].hidden_size, lstms[0].num_layers
     cache = owner.__dict__.setdefault('_proj_ops', {})
     outs = []
-    with torch.cuda.device(x.device):
-        x2 = x.reshape(N * T, -1)
+    with torch.cuda.device(dev):
         if engine == 'umma':
             op = cache.get('l0')
             if op is None:
                 op = cache['l0'] = LinearOperand(lambda: [(_lstm_layer_params(m, 0)[0], _lstm_layer_params(m, 0)[2])
                                                           for m in lstms])
-            pre = op(x2)                                               # [N*T, len(lstms) * 4H]
+            if len(parts) == 1:
+                pre = op(parts[0].reshape(N * T, -1))                  # [N*T, len(lstms) * 4H]
+            else:
+                pre = torch.empty((N * T, len(lstms) * 4 * H), device=dev, dtype=torch.float32)
+                r0 = 0
+                for p in parts:
+                    rows = p.shape[0] * T
+                    op(p.reshape(rows, -1), out=pre[r0:r0 + rows])
+                    r0 += rows
         else:
+            x2 = torch.cat(parts, 0).reshape(N * T, -1) if len(parts) > 1 else parts[0].reshape(N * T, -1)
             pre = torch.cat([F.linear(x2, _lstm_layer_params(m, 0)[0],
                                       sum(_lstm_layer_params(m, 0)[2]) if m.bias else None) for m in lstms], 1)
         first = None
         if len(lstms) == 2:
             # both time loops in one launch (grid.y = LSTM)
-            first = [torch.empty((N, T, H), device=x.device, dtype=torch.float32) for _ in lstms]
+            first = [torch.empty((N, T, H), device=dev, dtype=torch.float32) for _ in lstms]
             with _abi.stage('lstm'):
                 _abi.check(_abi.lib().se_lstm_rec_pair_fwd(
                     _abi.ptr(pre), pre.stride(0), _abi.ptr(_lstm_layer_params(lstms[0], 0)[1].contiguous()),
@@ -129,6 +142,13 @@ class ComplexLSTM(nn.Module):
         real, imag = split_complex(x, dim=-1)
         # both inputs share each LSTM's weights: run them stacked on the batch axis (2 calls, not 4)
         bdim = 0 if self.real_lstm.batch_first else 1
+        if (self.rec_kernel and self.proj_engine == 'umma' and self.real_lstm.batch_first and x.dim() == 3
+                and x.is_contiguous() and _lstm_rec_ok(self.real_lstm, x)):
+            # contiguous batch-first input: the two halves are projected in place (row stride 2*in), no stacked copy
+            by_real, by_imag = lstm_pair_forward(self, [self.real_lstm, self.imag_lstm], [real, imag], self.proj_engine)
+            r2r, i2r = torch.chunk(by_real, 2, dim=0)
+            r2i, i2i = torch.chunk(by_imag, 2, dim=0)
+            return merge_real_imag(x, r2r - i2i, r2i + i2r, dim=-1)
         both = torch.cat([real, imag], dim=bdim)
         if self.rec_kernel and _lstm_rec_ok(self.real_lstm, both):
             bf = self.real_lstm.batch_first

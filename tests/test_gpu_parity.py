@@ -452,6 +452,16 @@ def test_ccbam_on_cl2_matches_the_module_path(B, C, H, W):
     assert rel_l2(y.cpu(), want) < 2e-5                          # CL2 carries ~16 mantissa bits
 
 
+@pytest.mark.parametrize('B,C,F_,T', [(2, 256, 4, 37), (3, 128, 2, 50), (1, 32, 3, 5)])
+def test_cl2_from_lstm_rows_is_the_reference_permute(B, C, F_, T):
+    """[B, T, C*F] rows -> CL2 == permute(0, 2, 1).reshape(B, C, F, T) (dccrn.py:164-165) followed by the layout conversion"""
+    from speech_enhancement_b200 import chain
+    rows = rand((B, T, C * F_), 31, 1.0).to(DEV)
+    want = chain.cl2_from_nchw(rows.permute(0, 2, 1).reshape(B, C, F_, T).contiguous())
+    got = chain.cl2_from_lstm_rows(rows, B, C, F_, T)
+    assert got.data.shape == want.data.shape and torch.equal(got.data, want.data)
+
+
 def test_host_pipeline_overlapped_copies_give_the_same_waveforms():
     """HostPipeline (H2D / forward / D2H of neighbouring batches on three streams) == model(x)[1], batch by batch"""
     from speech_enhancement_b200.pipeline import HostPipeline
