@@ -114,6 +114,121 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Two gate columns per thread (2H threads).  ncu on the kernel above (profiles/r1f_lstm_full_summary.txt): the
+// shared-memory wavefront pipe is the limiter (79 % busy on the occupied SMs) -- per step and CTA 16 warps x 64
+// broadcast LDS.128 of h (two wavefronts each: a broadcast wavefront carries 8 bytes) + the 128 KB of weights
+// that do not fit the register file.  Halving the thread count halves the h wavefronts (every h value now
+// feeds two columns) and leaves 2 x KR <= 192 weight registers per thread, so only (H - KR) / H of the matrix
+// is re-read from shared memory each step.  Thread j owns columns j (gate i or f) and j + 2H (gate g or o);
+// the cell update runs on all 2H threads ((row, unit) pairs) instead of H.
+template <int H, int KR, int R>
+__global__ void __launch_bounds__(2 * H, 1)
+lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, const float* __restrict__ w_hh1,
+                 float* __restrict__ h_out0, float* __restrict__ h_out1, int64_t N, int64_t T, int64_t pre_ld) {
+  constexpr int G = 4 * H, NT = 2 * H, KS = H - KR;
+  constexpr int PER = (R * H + NT - 1) / NT;         // (row, unit) cells per thread
+  const float* __restrict__ w_hh = blockIdx.y ? w_hh1 : w_hh0;
+  float* __restrict__ h_out = blockIdx.y ? h_out1 : h_out0;
+  pre += blockIdx.y * G;
+  extern __shared__ __align__(16) float smem[];
+  float2* w_s = reinterpret_cast<float2*>(smem);     // [KS][NT] (column j, column j + NT)
+  float* h_s = smem + 2 * KS * NT;                   // [R][H]
+  float* g_s = h_s + R * H;                          // [R][G]
+  const int j = threadIdx.x;
+  const bool b_tanh = j < H;                         // column j + NT is gate g (tanh) for j < H, gate o otherwise
+
+  float wa[KR], wb[KR];
+#pragma unroll
+  for (int k = 0; k < KR; ++k) {
+    wa[k] = __ldg(w_hh + (int64_t)j * H + k);
+    wb[k] = __ldg(w_hh + (int64_t)(j + NT) * H + k);
+  }
+  for (int k = 0; k < KS; ++k)
+    w_s[k * NT + j] = make_float2(__ldg(w_hh + (int64_t)j * H + KR + k), __ldg(w_hh + (int64_t)(j + NT) * H + KR + k));
+
+  for (int64_t row0 = (int64_t)blockIdx.x * R; row0 < N; row0 += (int64_t)gridDim.x * R) {
+    float c[PER];
+#pragma unroll
+    for (int q = 0; q < PER; ++q) c[q] = 0.f;
+    const float* prow[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int64_t row = row0 + r < N ? row0 + r : N - 1;       // tail rows recompute the last row (never stored)
+      prow[r] = pre + row * T * pre_ld + j;
+    }
+    for (int i = j; i < R * H; i += NT) h_s[i] = 0.f;
+    float nxa[R], nxb[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) { nxa[r] = __ldg(prow[r]); nxb[r] = __ldg(prow[r] + NT); }
+    __syncthreads();
+    for (int64_t t = 0; t < T; ++t) {
+      float aa[R][2], ab[R][2];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        aa[r][0] = nxa[r]; aa[r][1] = 0.f;
+        ab[r][0] = nxb[r]; ab[r][1] = 0.f;
+        if (t + 1 < T) {
+          nxa[r] = __ldg(prow[r] + (t + 1) * pre_ld);
+          nxb[r] = __ldg(prow[r] + (t + 1) * pre_ld + NT);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < KR; k += 4) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const float4 hv = *reinterpret_cast<const float4*>(h_s + r * H + k);
+          aa[r][0] = fmaf(wa[k], hv.x, aa[r][0]);
+          aa[r][1] = fmaf(wa[k + 1], hv.y, aa[r][1]);
+          aa[r][0] = fmaf(wa[k + 2], hv.z, aa[r][0]);
+          aa[r][1] = fmaf(wa[k + 3], hv.w, aa[r][1]);
+          ab[r][0] = fmaf(wb[k], hv.x, ab[r][0]);
+          ab[r][1] = fmaf(wb[k + 1], hv.y, ab[r][1]);
+          ab[r][0] = fmaf(wb[k + 2], hv.z, ab[r][0]);
+          ab[r][1] = fmaf(wb[k + 3], hv.w, ab[r][1]);
+        }
+      }
+#pragma unroll 2
+      for (int k = 0; k < KS; k += 4) {
+        const float2 w0 = w_s[(k + 0) * NT + j], w1 = w_s[(k + 1) * NT + j];
+        const float2 w2 = w_s[(k + 2) * NT + j], w3 = w_s[(k + 3) * NT + j];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const float4 hv = *reinterpret_cast<const float4*>(h_s + r * H + KR + k);
+          aa[r][0] = fmaf(w0.x, hv.x, aa[r][0]);
+          aa[r][1] = fmaf(w1.x, hv.y, aa[r][1]);
+          aa[r][0] = fmaf(w2.x, hv.z, aa[r][0]);
+          aa[r][1] = fmaf(w3.x, hv.w, aa[r][1]);
+          ab[r][0] = fmaf(w0.y, hv.x, ab[r][0]);
+          ab[r][1] = fmaf(w1.y, hv.y, ab[r][1]);
+          ab[r][0] = fmaf(w2.y, hv.z, ab[r][0]);
+          ab[r][1] = fmaf(w3.y, hv.w, ab[r][1]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float a = aa[r][0] + aa[r][1], b = ab[r][0] + ab[r][1];
+        g_s[r * G + j] = sigmoidf_(a);
+        g_s[r * G + NT + j] = b_tanh ? tanhf_(b) : sigmoidf_(b);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int q = 0; q < PER; ++q) {
+        const int idx = j + q * NT;
+        if (idx < R * H) {
+          const int r = idx / H, u = idx - r * H;
+          const float* g = g_s + r * G;
+          c[q] = g[H + u] * c[q] + g[u] * g[2 * H + u];
+          const float h = g[3 * H + u] * tanhf_(c[q]);
+          h_s[idx] = h;
+          if (row0 + r < N) h_out[((row0 + r) * T + t) * H + u] = h;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Cluster version (H = 128): the 512 gate columns of a row are split over a 2-CTA cluster -- CTA r owns
 // hidden units [64r, 64r+64) x 4 gates = 256 columns x 128 k = 32 K weights, ALL of them in registers
 // (512 threads x 64), so a step reads no weights from shared memory at all (the single-CTA kernel above
@@ -255,6 +370,23 @@ static int launch_lstm_cluster(const float* pre, int64_t pre_ld, const float* w0
 }
 
 template <int H, int KR, int R>
+static int launch_lstm2(const float* pre, int64_t pre_ld, const float* w_hh0, const float* w_hh1, float* h_out0,
+                        float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
+  constexpr int G = 4 * H;
+  const int smem = ((H - KR) * G + R * H + R * G) * (int)sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    SE_CUDA(cudaFuncSetAttribute(lstm_rec2_kernel<H, KR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  int64_t ctas = (N + R - 1) / R;
+  if (ctas * nl > num_sms()) ctas = num_sms() / nl;
+  lstm_rec2_kernel<H, KR, R><<<dim3((unsigned)ctas, (unsigned)nl), 2 * H, smem, s>>>(pre, w_hh0, w_hh1, h_out0, h_out1,
+                                                                                      N, T, pre_ld);
+  return check_launch("lstm_rec2_kernel");
+}
+
+template <int H, int KR, int R>
 static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh0, const float* w_hh1, float* h_out0,
                        float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
   constexpr int G = 4 * H;
@@ -279,6 +411,16 @@ template <int H, int KR>
 static int dispatch_rows(const float* pre, int64_t pre_ld, const float* w0, const float* w1, float* h0, float* h1, int nl,
                          int64_t N, int64_t T, cudaStream_t s) {
   const int64_t sms = se::num_sms(), jobs = N * nl;
+  if (H == 128) {
+    // two columns per thread (see lstm_rec2_kernel); SE_LSTM_COLS=1 keeps the one-column kernel (tuning aid)
+    static const char* cols = getenv("SE_LSTM_COLS");
+    if (!(cols && atoi(cols) == 1)) {
+      constexpr int H2 = 128, KR2 = 96;                          // only instantiated for H = 128
+      if (jobs <= sms) return se::launch_lstm2<H2, KR2, 1>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+      if (jobs <= 2 * sms) return se::launch_lstm2<H2, KR2, 2>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+      return se::launch_lstm2<H2, KR2, 4>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+    }
+  }
   if (jobs <= sms) return se::launch_lstm<H, KR, 1>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
   if (jobs <= 2 * sms) return se::launch_lstm<H, KR, 2>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
   return se::launch_lstm<H, KR, 4>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
@@ -359,6 +501,51 @@ cl2_from_lstm_rows_kernel(const float* __restrict__ rows, int64_t ld, int C, int
     *reinterpret_cast<uint4*>(dst + plane) = *reinterpret_cast<const uint4*>(lo);
   }
 }
+
+// compile-time F: a thread owns 8 channels of one (b, t) row for every f -- its 8 F input floats are contiguous
+// (128 bytes for F = 4), the F stores of a warp are 512-byte runs; no shared memory
+template <int F>
+__global__ void __launch_bounds__(256)
+cl2_from_lstm_rows_f_kernel(const float* __restrict__ rows, int64_t ld, int64_t nrows, int C, int T, int Cp,
+                            __nv_bfloat16* __restrict__ out) {
+  const int groups = Cp / 8;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nrows * groups) return;
+  const int64_t r = i / groups;
+  const int c0 = (int)(i - r * groups) * 8;
+  const int64_t b = r / T;
+  const int t = (int)(r - b * T);
+  const int64_t plane = (int64_t)F * T * Cp;
+  __nv_bfloat16* dst = out + (b * 2) * plane + (int64_t)t * Cp + c0;
+  float v[8 * F];
+  if (c0 < C) {                                      // C / 2 is a multiple of 8: the group lies in one complex half
+    const int part = c0 >= C / 2, c = c0 - part * (C / 2);
+    const float4* src = reinterpret_cast<const float4*>(rows + r * ld + (int64_t)part * (C / 2) * F + (int64_t)c * F);
+#pragma unroll
+    for (int j = 0; j < 2 * F; ++j) {
+      const float4 q = __ldg(src + j);
+      v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8 * F; ++j) v[j] = 0.f;
+  }
+#pragma unroll
+  for (int f = 0; f < F; ++f) {
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float a0 = v[(2 * j) * F + f], a1 = v[(2 * j + 1) * F + f];
+      const __nv_bfloat162 h2 = __floats2bfloat162_rn(a0, a1);
+      const float2 hf = __bfloat1622float2(h2);
+      const __nv_bfloat162 l2 = __floats2bfloat162_rn(a0 - hf.x, a1 - hf.y);
+      hi[j] = *reinterpret_cast<const uint32_t*>(&h2);
+      lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
+    }
+    *reinterpret_cast<uint4*>(dst + (int64_t)f * T * Cp) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(dst + plane + (int64_t)f * T * Cp) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+}
 }  // namespace se
 
 extern "C" int se_cl2_from_lstm_rows(const float* rows, int64_t ld, int64_t B, int C, int F, int T, void* cl2, int Cp,
@@ -369,6 +556,18 @@ extern "C" int se_cl2_from_lstm_rows(const float* rows, int64_t ld, int64_t B, i
   if ((int64_t)C * F > 8192) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_lstm_rows: needs C * F <= 8192");
   if (B * T > 0x7fffffffll) return se::fail(SE_ERR_UNSUPPORTED, "se_cl2_from_lstm_rows: too many rows");
   if (B == 0) return SE_OK;
+  // fast path: 8-channel groups inside one complex half, 16-byte aligned 8*F-float runs
+  if ((F == 2 || F == 4) && (C / 2) % 8 == 0 && ld % 4 == 0 && (reinterpret_cast<uintptr_t>(rows) & 15) == 0) {
+    const int64_t total = B * T * (Cp / 8);
+    const unsigned blocks = (unsigned)((total + 255) / 256);
+    if (F == 4)
+      se::cl2_from_lstm_rows_f_kernel<4><<<blocks, 256, 0, (cudaStream_t)stream>>>(rows, ld, B * T, C, T, Cp,
+                                                                                   reinterpret_cast<__nv_bfloat16*>(cl2));
+    else
+      se::cl2_from_lstm_rows_f_kernel<2><<<blocks, 256, 0, (cudaStream_t)stream>>>(rows, ld, B * T, C, T, Cp,
+                                                                                   reinterpret_cast<__nv_bfloat16*>(cl2));
+    return se::check_launch("se_cl2_from_lstm_rows");
+  }
   se::cl2_from_lstm_rows_kernel<<<(unsigned)(B * T), 128, (size_t)C * F * sizeof(float), (cudaStream_t)stream>>>(
       rows, ld, C, F, T, Cp, reinterpret_cast<__nv_bfloat16*>(cl2));
   return se::check_launch("se_cl2_from_lstm_rows");

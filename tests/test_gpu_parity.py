@@ -452,7 +452,7 @@ def test_ccbam_on_cl2_matches_the_module_path(B, C, H, W):
     assert rel_l2(y.cpu(), want) < 2e-5                          # CL2 carries ~16 mantissa bits
 
 
-@pytest.mark.parametrize('B,C,F_,T', [(2, 256, 4, 37), (3, 128, 2, 50), (1, 32, 3, 5)])
+@pytest.mark.parametrize('B,C,F_,T', [(2, 256, 4, 37), (3, 128, 2, 50), (1, 32, 3, 5), (2, 80, 4, 9), (1, 16, 2, 300), (2, 24, 4, 7)])
 def test_cl2_from_lstm_rows_is_the_reference_permute(B, C, F_, T):
     """[B, T, C*F] rows -> CL2 == permute(0, 2, 1).reshape(B, C, F, T) (dccrn.py:164-165) followed by the layout conversion"""
     from speech_enhancement_b200 import chain
