@@ -114,69 +114,79 @@ lstm_rec_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Two gate columns per thread (2H threads).  ncu on the kernel above (profiles/r1f_lstm_full_summary.txt): the
-// shared-memory wavefront pipe is the limiter (79 % busy on the occupied SMs) -- per step and CTA 16 warps x 64
-// broadcast LDS.128 of h (two wavefronts each: a broadcast wavefront carries 8 bytes) + the 128 KB of weights
-// that do not fit the register file.  Halving the thread count halves the h wavefronts (every h value now
-// feeds two columns) and leaves 2 x KR <= 192 weight registers per thread, so only (H - KR) / H of the matrix
-// is re-read from shared memory each step.  Thread j owns columns j (gate i or f) and j + 2H (gate g or o);
-// the cell update runs on all 2H threads ((row, unit) pairs) instead of H.
+// Two gate columns per thread (2H threads), the production kernel for H = 128.  ncu on the one-column kernel above
+// (profiles/r1f_lstm_full_summary.txt): the shared-memory wavefront pipe is the limiter (79 % busy on the occupied
+// SMs) -- per step and CTA 16 warps x 64 broadcast LDS.128 of h (two wavefronts each: a broadcast wavefront carries
+// 8 bytes) + the 128 KB of weights that do not fit the register file.  Halving the thread count halves the h
+// wavefronts (every h value now feeds two columns) and leaves 2 x KR = 192 weight registers per thread, so only
+// (H - KR) / H = 1/4 of the matrix is re-read from shared memory each step.
+// The four gates of a hidden unit live in ONE warp: lanes 0-15 of warp w own (i, g) of units 16w .. 16w+15, lanes
+// 16-31 own (f, o) of the same units.  The cell update then needs three shuffles instead of a round trip through
+// shared memory, every lane runs exactly one tanh(c) per row pair (upper half: even rows, lower half: odd rows),
+// h is double-buffered and a step costs ONE __syncthreads.  sigmoid(x) is evaluated as 0.5 + 0.5 tanh(x / 2) so
+// that the mixed-gate warps do not diverge.  (64 x 4 s DCCRN batch: 1.40 -> 1.06 -> 0.90 ms per launch.)
 template <int H, int KR, int R>
 __global__ void __launch_bounds__(2 * H, 1)
 lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0, const float* __restrict__ w_hh1,
                  float* __restrict__ h_out0, float* __restrict__ h_out1, int64_t N, int64_t T, int64_t pre_ld) {
-  constexpr int G = 4 * H, NT = 2 * H, KS = H - KR;
-  constexpr int PER = (R * H + NT - 1) / NT;         // (row, unit) cells per thread
+  constexpr int NT = 2 * H, KS = H - KR, RP = (R + 1) / 2;
   const float* __restrict__ w_hh = blockIdx.y ? w_hh1 : w_hh0;
   float* __restrict__ h_out = blockIdx.y ? h_out1 : h_out0;
-  pre += blockIdx.y * G;
+  pre += blockIdx.y * 4 * H;
   extern __shared__ __align__(16) float smem[];
-  float2* w_s = reinterpret_cast<float2*>(smem);     // [KS][NT] (column j, column j + NT)
-  float* h_s = smem + 2 * KS * NT;                   // [R][H]
-  float* g_s = h_s + R * H;                          // [R][G]
-  const int j = threadIdx.x;
-  const bool b_tanh = j < H;                         // column j + NT is gate g (tanh) for j < H, gate o otherwise
+  float2* w_s = reinterpret_cast<float2*>(smem);     // [KS][NT] (column ca, column cb of thread j)
+  float* h_s = smem + 2 * KS * NT;                   // [2][R][H]
+  const int j = threadIdx.x, lane = j & 31;
+  const bool upper = lane >= 16;
+  const int u = 16 * (j >> 5) + (lane & 15);
+  const int ca = (upper ? H : 0) + u;                // i | f
+  const int cb = ca + 2 * H;                         // g | o
+  const float bs = upper ? 0.5f : 1.f, bo = upper ? 0.5f : 0.f;   // act(b) = bo + bs * tanh(bs * b)
 
   float wa[KR], wb[KR];
 #pragma unroll
   for (int k = 0; k < KR; ++k) {
-    wa[k] = __ldg(w_hh + (int64_t)j * H + k);
-    wb[k] = __ldg(w_hh + (int64_t)(j + NT) * H + k);
+    wa[k] = __ldg(w_hh + (int64_t)ca * H + k);
+    wb[k] = __ldg(w_hh + (int64_t)cb * H + k);
   }
   for (int k = 0; k < KS; ++k)
-    w_s[k * NT + j] = make_float2(__ldg(w_hh + (int64_t)j * H + KR + k), __ldg(w_hh + (int64_t)(j + NT) * H + KR + k));
+    w_s[k * NT + j] = make_float2(__ldg(w_hh + (int64_t)ca * H + KR + k), __ldg(w_hh + (int64_t)cb * H + KR + k));
 
   for (int64_t row0 = (int64_t)blockIdx.x * R; row0 < N; row0 += (int64_t)gridDim.x * R) {
-    float c[PER];
+    float c[RP];
 #pragma unroll
-    for (int q = 0; q < PER; ++q) c[q] = 0.f;
+    for (int q = 0; q < RP; ++q) c[q] = 0.f;
     const float* prow[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const int64_t row = row0 + r < N ? row0 + r : N - 1;       // tail rows recompute the last row (never stored)
-      prow[r] = pre + row * T * pre_ld + j;
+      prow[r] = pre + row * T * pre_ld;
     }
+    __syncthreads();                                             // previous row block is done with h_s
     for (int i = j; i < R * H; i += NT) h_s[i] = 0.f;
     float nxa[R], nxb[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) { nxa[r] = __ldg(prow[r]); nxb[r] = __ldg(prow[r] + NT); }
+    for (int r = 0; r < R; ++r) { nxa[r] = __ldg(prow[r] + ca); nxb[r] = __ldg(prow[r] + cb); }
     __syncthreads();
+    int cur = 0;
     for (int64_t t = 0; t < T; ++t) {
+      const float* hc = h_s + cur * (R * H);
+      float* hn = h_s + (cur ^ 1) * (R * H);
       float aa[R][2], ab[R][2];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         aa[r][0] = nxa[r]; aa[r][1] = 0.f;
         ab[r][0] = nxb[r]; ab[r][1] = 0.f;
         if (t + 1 < T) {
-          nxa[r] = __ldg(prow[r] + (t + 1) * pre_ld);
-          nxb[r] = __ldg(prow[r] + (t + 1) * pre_ld + NT);
+          nxa[r] = __ldg(prow[r] + (t + 1) * pre_ld + ca);
+          nxb[r] = __ldg(prow[r] + (t + 1) * pre_ld + cb);
         }
       }
 #pragma unroll
       for (int k = 0; k < KR; k += 4) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const float4 hv = *reinterpret_cast<const float4*>(h_s + r * H + k);
+          const float4 hv = *reinterpret_cast<const float4*>(hc + r * H + k);
           aa[r][0] = fmaf(wa[k], hv.x, aa[r][0]);
           aa[r][1] = fmaf(wa[k + 1], hv.y, aa[r][1]);
           aa[r][0] = fmaf(wa[k + 2], hv.z, aa[r][0]);
@@ -193,7 +203,7 @@ lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0,
         const float2 w2 = w_s[(k + 2) * NT + j], w3 = w_s[(k + 3) * NT + j];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const float4 hv = *reinterpret_cast<const float4*>(h_s + r * H + KR + k);
+          const float4 hv = *reinterpret_cast<const float4*>(hc + r * H + KR + k);
           aa[r][0] = fmaf(w0.x, hv.x, aa[r][0]);
           aa[r][1] = fmaf(w1.x, hv.y, aa[r][1]);
           aa[r][0] = fmaf(w2.x, hv.z, aa[r][0]);
@@ -204,26 +214,32 @@ lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0,
           ab[r][1] = fmaf(w3.y, hv.w, ab[r][1]);
         }
       }
+      float ga[R], gb[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const float a = aa[r][0] + aa[r][1], b = ab[r][0] + ab[r][1];
-        g_s[r * G + j] = sigmoidf_(a);
-        g_s[r * G + NT + j] = b_tanh ? tanhf_(b) : sigmoidf_(b);
+        ga[r] = 0.5f + 0.5f * tanhf_(0.5f * (aa[r][0] + aa[r][1]));          // i | f
+        gb[r] = bo + bs * tanhf_(bs * (ab[r][0] + ab[r][1]));               // g | o
       }
-      __syncthreads();
 #pragma unroll
-      for (int q = 0; q < PER; ++q) {
-        const int idx = j + q * NT;
-        if (idx < R * H) {
-          const int r = idx / H, u = idx - r * H;
-          const float* g = g_s + r * G;
-          c[q] = g[H + u] * c[q] + g[u] * g[2 * H + u];
-          const float h = g[3 * H + u] * tanhf_(c[q]);
-          h_s[idx] = h;
+      for (int q = 0; q < RP; ++q) {
+        constexpr unsigned FULL = 0xffffffffu;
+        const int r0 = 2 * q, r1 = 2 * q + 1 < R ? 2 * q + 1 : 2 * q;
+        // even row r0: the upper half (f, o) receives i*g; odd row r1: the lower half (i, g) receives f and o
+        const float p0 = __shfl_xor_sync(FULL, ga[r0] * gb[r0], 16);
+        const float f1 = __shfl_xor_sync(FULL, ga[r1], 16);
+        const float o1 = __shfl_xor_sync(FULL, gb[r1], 16);
+        const float cn = upper ? fmaf(ga[r0], c[q], p0) : fmaf(f1, c[q], ga[r1] * gb[r1]);
+        const float og = upper ? gb[r0] : o1;
+        const int r = upper ? r0 : 2 * q + 1;
+        if (r < R) {
+          c[q] = cn;
+          const float h = og * tanhf_(cn);
+          hn[r * H + u] = h;
           if (row0 + r < N) h_out[((row0 + r) * T + t) * H + u] = h;
         }
       }
       __syncthreads();
+      cur ^= 1;
     }
   }
 }
@@ -372,8 +388,7 @@ static int launch_lstm_cluster(const float* pre, int64_t pre_ld, const float* w0
 template <int H, int KR, int R>
 static int launch_lstm2(const float* pre, int64_t pre_ld, const float* w_hh0, const float* w_hh1, float* h_out0,
                         float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
-  constexpr int G = 4 * H;
-  const int smem = ((H - KR) * G + R * H + R * G) * (int)sizeof(float);
+  const int smem = ((H - KR) * 4 * H + 2 * R * H) * (int)sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
     SE_CUDA(cudaFuncSetAttribute(lstm_rec2_kernel<H, KR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
