@@ -18,6 +18,7 @@ se_cconv_small_cin, se_cl2_from_nchw, se_cl2_to_nchw).
 """
 import ctypes as C
 
+import os
 import torch
 import torch.nn as nn
 
@@ -330,6 +331,18 @@ class RealConvBlock(FusedBlock):
         return w.reshape(w.shape[0], -1), b, w.shape[0] // 2, w.shape[1] // 2, w.shape[2], w.shape[3]
 
 
+# side streams for independent linear-projection launches (0: all on the current stream; SE_LINEAR_STREAMS overrides)
+FANOUT_STREAMS = int(os.environ.get('SE_LINEAR_STREAMS', '4'))
+_SIDE = {}
+
+
+def _side_streams(dev, n):
+    pool = _SIDE.setdefault(torch.device(dev).index if torch.device(dev).index is not None else torch.cuda.current_device(), [])
+    while len(pool) < n:
+        pool.append(torch.cuda.Stream(device=dev))
+    return pool[:n]
+
+
 class LinearOperand:
     """y = x W^T + b on the bf16x3 GEMM engine for one or several stacked nn.Linear-style weights
     (the LSTM input projections and ComplexLinear of /root/reference/models/modules/complex_nn.py:93-145).
@@ -379,19 +392,35 @@ class LinearOperand:
     def __call__(self, x, out=None, out_col=0):
         """x: [M, K] fp32 CUDA with unit column stride (row stride free).  Writes columns
         [out_col, out_col + N) of `out` ([M, >= out_col + N] fp32 contiguous; allocated when None)."""
-        ops = self._operands()
-        M, K = x.shape
-        N, Cp = ops['N'], ops['Cp']
-        if K != ops['K'] or x.stride(1) != 1 or x.dtype != torch.float32 or not x.is_cuda:
-            raise RuntimeError(f'LinearOperand: expected fp32 CUDA [M, {ops["K"]}] with unit column stride')
-        if out is None:
-            out = torch.empty((M, N), device=x.device, dtype=torch.float32)
-        ldo = out.stride(0)
-        if M == 0:
-            return out
-        H, W = (2, M // 2) if M % 2 == 0 else (1, M)       # two image rows let two accumulators share a weight unit
-        lib = _abi.lib()
-        with torch.cuda.device(x.device), _abi.stage('linear'):
+        return self.many([(x, out, out_col)])[0]
+
+    def many(self, jobs):
+        """several independent products [(x, out | None, out_col), ...] with this operand (see `linear_many`)"""
+        return linear_many([(self, x, out, col) for x, out, col in jobs])
+
+
+def linear_many(jobs):
+    """Several independent products [(operand, x, out | None, out_col), ...].  Every (job, <= 256-column
+    chunk) pair is its own persistent GEMM launch of one CTA per SM whose last wave is mostly empty (161 tiles on
+    148 SMs for the DCCRN LSTM projection), so the launches are dealt round-robin to side streams and the block
+    scheduler fills the idle SMs of one launch's tail with the next launch's CTAs; joined before returning."""
+    lib = _abi.lib()
+    outs, launches = [], []
+    dev = jobs[0][1].device
+    with torch.cuda.device(dev), _abi.stage('linear'):
+        for op, x, out, out_col in jobs:
+            ops = op._operands()
+            N, Cp = ops['N'], ops['Cp']
+            M, K = x.shape
+            if K != ops['K'] or x.stride(1) != 1 or x.dtype != torch.float32 or not x.is_cuda:
+                raise RuntimeError(f'LinearOperand: expected fp32 CUDA [M, {ops["K"]}] with unit column stride')
+            if out is None:
+                out = torch.empty((M, N), device=x.device, dtype=torch.float32)
+            outs.append(out)
+            if M == 0:
+                continue
+            ldo = out.stride(0)
+            H, W = (2, M // 2) if M % 2 == 0 else (1, M)   # two image rows let two accumulators share a weight unit
             img = torch.empty((1, 2, H, W, Cp), device=x.device, dtype=torch.bfloat16)
             _abi.check(lib.se_cl2_from_rows(_abi.ptr(x), M, K, x.stride(0), _abi.ptr(img), Cp, _abi.stream_ptr()))
             for c0, n, wq in ops['chunks']:
@@ -403,5 +432,20 @@ class LinearOperand:
                 a.wq, a.bias, a.slope = wq.data_ptr(), ops['bias'].data_ptr() + 4 * c0, 1.0
                 a.y_nchw = out.data_ptr() + 4 * (out_col + c0)
                 a.y_cs, a.y_ws, a.y_hs = 1, ldo, W * ldo
+                launches.append((a, img))
+        if len(launches) <= 1 or not FANOUT_STREAMS:
+            for a, _ in launches:
                 _abi.check(lib.se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
-        return out
+        else:
+            cur = torch.cuda.current_stream(dev)
+            side = _side_streams(dev, min(FANOUT_STREAMS, len(launches)))
+            fork = torch.cuda.Event()
+            fork.record(cur)
+            for i, (a, _) in enumerate(launches):
+                s = side[i % len(side)]
+                if i < len(side):
+                    s.wait_event(fork)
+                _abi.check(lib.se_cconv_gemm(C.byref(a), C.c_void_p(s.cuda_stream)))
+            for s in side:
+                cur.wait_stream(s)                          # `img` / `out` are next touched on `cur`, after the join
+    return outs

@@ -62,11 +62,12 @@ def lstm_pair_forward(owner, lstms, x, engine):
                 pre = op(parts[0].reshape(N * T, -1))                  # [N*T, len(lstms) * 4H]
             else:
                 pre = torch.empty((N * T, len(lstms) * 4 * H), device=dev, dtype=torch.float32)
-                r0 = 0
+                r0, jobs = 0, []
                 for p in parts:
                     rows = p.shape[0] * T
-                    op(p.reshape(rows, -1), out=pre[r0:r0 + rows])
+                    jobs.append((p.reshape(rows, -1), pre[r0:r0 + rows], 0))
                     r0 += rows
+                op.many(jobs)
         else:
             x2 = torch.cat(parts, 0).reshape(N * T, -1) if len(parts) > 1 else parts[0].reshape(N * T, -1)
             pre = torch.cat([F.linear(x2, _lstm_layer_params(m, 0)[0],
@@ -121,8 +122,8 @@ class ComplexLinear(nn.Module):
             if x2.stride(1) != 1:
                 x2 = x2.contiguous()
             out = torch.empty((x2.shape[0], 2 * No), device=x.device, dtype=torch.float32)
-            ops[0](x2[:, :K], out=out, out_col=0)
-            ops[1](x2[:, K:], out=out, out_col=No)
+            from ..chain import linear_many
+            linear_many([(ops[0], x2[:, :K], out, 0), (ops[1], x2[:, K:], out, No)])
             return out.reshape(*x.shape[:-1], 2 * No)
         real, imag = split_complex(x, dim=-1)
         return merge_real_imag(x, self.real_linear(real), self.imag_linear(imag), dim=-1)
