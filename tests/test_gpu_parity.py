@@ -712,3 +712,33 @@ def test_cuda_graph_replay_matches_eager(cls, args, B, L):
         spec_g, wav_g = g(x)
         assert torch.equal(wav_g, wav_e) and torch.equal(spec_g, spec_e)
     assert len(g._graphs) == 1
+
+
+@pytest.mark.parametrize('B,H,W,CO,kh,kw,sh,sw,ph,pw,oph,opw', [
+    (2, 16, 37, 2, 5, 2, 2, 1, 2, 0, 1, 0),      # DCCRN last decoder layer (_2008_00264_dccrn.py:104-111)
+    (1, 33, 70, 2, 7, 1, 1, 1, 3, 0, 0, 0),      # DCUNet last decoder layer (_1903_03107_dcunet.py:79-81)
+    (3, 9, 11, 4, 3, 3, 2, 2, 1, 1, 1, 1),
+    (1, 70, 130, 2, 5, 3, 2, 2, 2, 1, 0, 0),     # several tiles in both directions
+    (2, 5, 3, 4, 1, 2, 1, 1, 0, 0, 0, 0),
+])
+def test_col2im_gathers_every_tap_product(B, H, W, CO, kh, kw, sh, sw, ph, pw, oph, opw):
+    """se_cconvT_col2im: y[b, co, hi*sh - ph + dh, wi*sw - pw + dw] += P[b, hi, wi, (dh*kw + dw)*CO + co], + bias, LeakyReLU"""
+    from speech_enhancement_b200 import _abi
+    Ho, Wo = (H - 1) * sh - 2 * ph + kh + oph, (W - 1) * sw - 2 * pw + kw + opw
+    ncol = kh * kw * CO
+    Np = (ncol + 3) // 4 * 4
+    P = rand((B, H, W, Np), 77, 1.0).to(DEV)
+    bias = rand((CO,), 78, 1.0).to(DEV)
+    slope = 0.25
+    y = torch.full((B, CO, Ho, Wo), float('nan'), device=DEV)
+    _abi.check(_abi.lib().se_cconvT_col2im(_abi.ptr(P), B, H, W, Np, CO, kh, kw, sh, sw, ph, pw, Ho, Wo, _abi.ptr(bias),
+                                           slope, _abi.ptr(y), _abi.stream_ptr()))
+    want = torch.zeros((B, CO, Ho + 2 * ph + kh, Wo + 2 * pw + kw), device=DEV, dtype=torch.float64)
+    for dh in range(kh):
+        for dw in range(kw):
+            t = (dh * kw + dw) * CO
+            want[:, :, dh:dh + (H - 1) * sh + 1:sh, dw:dw + (W - 1) * sw + 1:sw] += P[..., t:t + CO].permute(0, 3, 1, 2).double()
+    want = want[:, :, ph:ph + Ho, pw:pw + Wo] + bias.double().view(1, CO, 1, 1)
+    want = torch.where(want > 0, want, want * slope).float()
+    assert torch.isfinite(y).all()
+    assert (y - want).abs().max().item() <= 2e-6 * max(1.0, want.abs().max().item())
