@@ -14,7 +14,7 @@ echo "ncu gemm rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:lstm_rec -s 4 -c 2 \
   -o gpurun_out/${tag}_lstm_full -f python bench.py --steps 2 --warmup 3 > gpurun_out/${tag}_ncu_lstm.log 2>&1
 echo "ncu lstm rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'fft_kernel|mask_kernel|small_cin|col2im' -s 16 -c 5 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'fft_kernel|mask_kernel|cconv_first|col2im|cl2_from_lstm_rows' -s 18 -c 6 \
   -o gpurun_out/${tag}_hbm_full -f python bench.py --steps 2 --warmup 3 > gpurun_out/${tag}_ncu_hbm.log 2>&1
 echo "ncu hbm rc=$?"; ls -la gpurun_out/${tag}_*.ncu-rep
 for m in dccrn dcunet20 frcrn; do timeout 300 python scripts/chain_layers.py --model $m; done > gpurun_out/${tag}_chain_layers.txt 2>&1
