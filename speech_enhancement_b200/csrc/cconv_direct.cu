@@ -113,7 +113,10 @@ __device__ __forceinline__ void st_global_v8(void* ptr, const uint32_t* v) {
                : "memory");
 }
 
-template <int KH, int KW, int SH, int SW>
+// PX output pixels per thread: every broadcast LDS.128 of four weights (two shared-memory wavefronts) feeds 4 * PX FMAs.
+// Measured at 64 x 4 s: PX = 2 wins where the weight reads dominate (Cout2 = 64: 1.15 -> 0.99 ms, 128: 1.14 -> 0.97 ms)
+// and loses where the CL2 stores do (Cout2 = 32, half of the 128-byte rows is channel padding: 0.50 -> 0.56 ms).
+template <int KH, int KW, int SH, int SW, int PX>
 __global__ void __launch_bounds__(128)
 cconv_first_kernel(const SmallCinParams p) {
   constexpr int CIN2 = 2, K = CIN2 * KH * KW;
@@ -126,15 +129,21 @@ cconv_first_kernel(const SmallCinParams p) {
   }
   for (int i = threadIdx.x; i < Cr; i += blockDim.x) b_s[i] = (i < p.Cout2 && p.bias != nullptr) ? __ldg(p.bias + i) : 0.f;
   __syncthreads();
-  // 128 consecutive output pixels of one image per block (rows are not padded to the block size)
+  // PX * 128 consecutive output pixels of one image per block (rows are not padded to the block size); thread t owns
+  // pixels base + t, base + 128 + t, ...
   const int64_t plane = (int64_t)p.Ho * p.Wo;
-  const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t pix0 = (int64_t)blockIdx.x * (blockDim.x * PX) + threadIdx.x;
   const int64_t b = blockIdx.y;
-  if (pix >= plane) return;
-  const int ho = (int)(pix / p.Wo), wo = (int)(pix - (int64_t)ho * p.Wo);
+  if (pix0 >= plane) return;
 
-  float xk[K];
-  {
+  float xk[PX][K];
+  bool ok[PX];
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    const int64_t pix = pix0 + (int64_t)i * blockDim.x;
+    ok[i] = pix < plane;
+    const int64_t pc = ok[i] ? pix : pix0;
+    const int ho = (int)(pc / p.Wo), wo = (int)(pc - (int64_t)ho * p.Wo);
     const int h0 = ho * SH - p.ph - p.pad_top, w0 = wo * SW - p.pw - p.pad_left;
     const float* xb = p.x + b * p.xs_b;
 #pragma unroll
@@ -147,20 +156,22 @@ cconv_first_kernel(const SmallCinParams p) {
 #pragma unroll
         for (int dw = 0; dw < KW; ++dw) {
           const int w = w0 + dw;
-          xk[(c * KH + dh) * KW + dw] = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + dw) : 0.f;
+          xk[i][(c * KH + dh) * KW + dw] = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + dw) : 0.f;
         }
       }
   }
   const float slope = p.slope;
-  __nv_bfloat16* cb = p.y_cl2 != nullptr ? p.y_cl2 + (b * 2 * plane + pix) * p.y_Cp : nullptr;
   for (int c0 = 0; c0 < Cr; c0 += 32) {
-    float acc[32];
+    float acc[PX][32];
     {
       const float4* br = reinterpret_cast<const float4*>(b_s + c0);
 #pragma unroll
       for (int j4 = 0; j4 < 8; ++j4) {
         const float4 b4 = br[j4];
-        acc[4 * j4] = b4.x; acc[4 * j4 + 1] = b4.y; acc[4 * j4 + 2] = b4.z; acc[4 * j4 + 3] = b4.w;
+#pragma unroll
+        for (int i = 0; i < PX; ++i) {
+          acc[i][4 * j4] = b4.x; acc[i][4 * j4 + 1] = b4.y; acc[i][4 * j4 + 2] = b4.z; acc[i][4 * j4 + 3] = b4.w;
+        }
       }
     }
 #pragma unroll
@@ -169,45 +180,58 @@ cconv_first_kernel(const SmallCinParams p) {
 #pragma unroll
       for (int j4 = 0; j4 < 8; ++j4) {
         const float4 w4 = wr[j4];
-        acc[4 * j4 + 0] = fmaf(w4.x, xk[k], acc[4 * j4 + 0]);
-        acc[4 * j4 + 1] = fmaf(w4.y, xk[k], acc[4 * j4 + 1]);
-        acc[4 * j4 + 2] = fmaf(w4.z, xk[k], acc[4 * j4 + 2]);
-        acc[4 * j4 + 3] = fmaf(w4.w, xk[k], acc[4 * j4 + 3]);
+#pragma unroll
+        for (int i = 0; i < PX; ++i) {
+          acc[i][4 * j4 + 0] = fmaf(w4.x, xk[i][k], acc[i][4 * j4 + 0]);
+          acc[i][4 * j4 + 1] = fmaf(w4.y, xk[i][k], acc[i][4 * j4 + 1]);
+          acc[i][4 * j4 + 2] = fmaf(w4.z, xk[i][k], acc[i][4 * j4 + 2]);
+          acc[i][4 * j4 + 3] = fmaf(w4.w, xk[i][k], acc[i][4 * j4 + 3]);
+        }
       }
     }
 #pragma unroll
-    for (int j = 0; j < 32; ++j) acc[j] = acc[j] > 0.f ? acc[j] : acc[j] * slope;
-    if (p.y != nullptr) {
+    for (int i = 0; i < PX; ++i) {
+      if (!ok[i]) continue;
+      const int64_t pix = pix0 + (int64_t)i * blockDim.x;
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc[j];
-    }
-    if (cb != nullptr) {
-      // channels >= Cout2 inside this pass carry zero weights and zero bias: they come out as exact zeros
-      uint32_t hi[16], lo[16];
+      for (int j = 0; j < 32; ++j) acc[i][j] = acc[i][j] > 0.f ? acc[i][j] : acc[i][j] * slope;
+      if (p.y != nullptr) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
-        const float2 hf = __bfloat1622float2(h2);
-        const __nv_bfloat162 l2 = __floats2bfloat162_rn(acc[2 * j] - hf.x, acc[2 * j + 1] - hf.y);
-        hi[j] = *reinterpret_cast<const uint32_t*>(&h2);
-        lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
+        for (int j = 0; j < 32; ++j)
+          if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc[i][j];
       }
-      // 32-byte stores: one full sector per lane and instruction (lanes are a pixel = 128+ bytes apart)
-      __nv_bfloat16* dh = cb + c0;
-      __nv_bfloat16* dl = cb + plane * p.y_Cp + c0;
+      if (p.y_cl2 != nullptr) {
+        // channels >= Cout2 inside this pass carry zero weights and zero bias: they come out as exact zeros
+        uint32_t hi[16], lo[16];
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        st_global_v8(dh + 16 * j, hi + 8 * j);
-        st_global_v8(dl + 16 * j, lo + 8 * j);
+        for (int j = 0; j < 16; ++j) {
+          const __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[i][2 * j], acc[i][2 * j + 1]);
+          const float2 hf = __bfloat1622float2(h2);
+          const __nv_bfloat162 l2 = __floats2bfloat162_rn(acc[i][2 * j] - hf.x, acc[i][2 * j + 1] - hf.y);
+          hi[j] = *reinterpret_cast<const uint32_t*>(&h2);
+          lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
+        }
+        // 32-byte stores: one full sector per lane and instruction (lanes are a pixel = 128+ bytes apart)
+        __nv_bfloat16* dh = p.y_cl2 + (b * 2 * plane + pix) * p.y_Cp + c0;
+        __nv_bfloat16* dl = dh + plane * p.y_Cp;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          st_global_v8(dh + 16 * j, hi + 8 * j);
+          st_global_v8(dl + 16 * j, lo + 8 * j);
+        }
       }
     }
   }
-  if (cb != nullptr) {                             // CL2 pad channels [Cr, y_Cp)
+  if (p.y_cl2 != nullptr) {                        // CL2 pad channels [Cr, y_Cp)
     const uint32_t z[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
-    for (int c0 = Cr; c0 < p.y_Cp; c0 += 16) {       // Cr and y_Cp are multiples of 32
-      st_global_v8(cb + c0, z);
-      st_global_v8(cb + plane * p.y_Cp + c0, z);
+#pragma unroll
+    for (int i = 0; i < PX; ++i) {
+      if (!ok[i]) continue;
+      __nv_bfloat16* cb = p.y_cl2 + (b * 2 * plane + pix0 + (int64_t)i * blockDim.x) * p.y_Cp;
+      for (int c0 = Cr; c0 < p.y_Cp; c0 += 16) {     // Cr and y_Cp are multiples of 32
+        st_global_v8(cb + c0, z);
+        st_global_v8(cb + plane * p.y_Cp + c0, z);
+      }
     }
   }
 }
@@ -216,8 +240,10 @@ template <int KH, int KW, int SH, int SW>
 static int launch_first(const SmallCinParams& p, int64_t B, cudaStream_t s) {
   const int Cr = (p.Cout2 + 31) / 32 * 32;
   const int smem = (2 * KH * KW * Cr + Cr) * 4;
-  dim3 grid((unsigned)(((int64_t)p.Ho * p.Wo + 127) / 128), (unsigned)B);
-  cconv_first_kernel<KH, KW, SH, SW><<<grid, 128, smem, s>>>(p);
+  const int px = Cr > 32 ? 2 : 1;
+  dim3 grid((unsigned)(((int64_t)p.Ho * p.Wo + 128 * px - 1) / (128 * px)), (unsigned)B);
+  if (px == 2) cconv_first_kernel<KH, KW, SH, SW, 2><<<grid, 128, smem, s>>>(p);
+  else cconv_first_kernel<KH, KW, SH, SW, 1><<<grid, 128, smem, s>>>(p);
   return check_launch("se_cconv_small_cin(first)");
 }
 
