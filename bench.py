@@ -449,7 +449,7 @@ def run_ours(args):
                 'frac': tflops / pk['bf16_tflops_sustained'],
                 # dram__bytes_read + write summed over the 11 conv GEMM launches of one step from the ncu --set full
                 # captures (profiles/r1c_gemm_full_summary.txt, B=64: 25.46 GB; the eight launches re-captured in
-                # profiles/r1e_gemm_full_summary.txt agree within 2 %), scaled per utterance
+                # profiles/r1e_gemm_full_summary.txt / r1g_gemm_full_summary.txt agree within 2 %), scaled per utterance
                 'traffic': 25.458e9 / 64 * B if args.model == 'dccrn' else None,
                 'traffic_unit': 'B per step (all conv GEMM launches)',
                 'peak_source': pk['source'] + ' bf16 dense (sustained)',

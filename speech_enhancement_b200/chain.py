@@ -333,6 +333,8 @@ class RealConvBlock(FusedBlock):
 
 # side streams for independent linear-projection launches (0: all on the current stream; SE_LINEAR_STREAMS overrides)
 FANOUT_STREAMS = int(os.environ.get('SE_LINEAR_STREAMS', '4'))
+# output columns per GEMM launch of a linear layer (<= 256: one accumulator's TMEM columns)
+LINEAR_CHUNK = int(os.environ.get('SE_LINEAR_CHUNK', '256'))
 _SIDE = {}
 
 
@@ -379,8 +381,8 @@ class LinearOperand:
                 chunks = []
                 lib = _abi.lib()
                 with torch.cuda.device(W.device):
-                    for c0 in range(0, N, 256):
-                        n = min(256, N - c0)
+                    for c0 in range(0, N, LINEAR_CHUNK):
+                        n = min(LINEAR_CHUNK, N - c0)
                         wq = torch.empty(lib.se_cconv_wq_elems(n, Cp, 1), device=W.device, dtype=torch.bfloat16)
                         _abi.check(lib.se_cconv_prep_weight(_abi.ptr(W[c0:c0 + n]), n, K, 1, None, Cp, _abi.ptr(wq),
                                                             _abi.stream_ptr()))
