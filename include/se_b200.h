@@ -156,6 +156,9 @@ typedef struct se_cconv_args {
    * own bottom / right edge -- the F.pad(x, ...) to the skip's size in front of the decoder layers
    * (_1903_03107_dcunet.py:89-92, _2206_07293_frcrn.py:97-98), done by TMA out-of-bounds fill.       */
   int src_H[2], src_W[2];
+  /* optional real channel count of every source (0 = src_Cp): channels [src_C, src_Cp) are zero in the CL2
+   * activations and in the prepared weights, so the engine skips 16-channel k-steps that are all padding. */
+  int src_C[2];
 } se_cconv_args;
 SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);
 /* fp32 x[b*xs_b + c*xs_c + h*xs_h + w] -> CL2 (same as se_cl2_from_nchw for arbitrary outer strides). */

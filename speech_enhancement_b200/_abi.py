@@ -80,7 +80,7 @@ class ConvArgs(C.Structure):
                 ('y_cl2', C.c_void_p), ('y_Cp', C.c_int),
                 ('y_bs', C.c_int64), ('y_cs', C.c_int64), ('y_hs', C.c_int64), ('y_ws', C.c_int64),
                 ('y_off', C.c_int64), ('y_lim', C.c_int64), ('y_scale', C.c_void_p),
-                ('src_H', C.c_int * 2), ('src_W', C.c_int * 2)]
+                ('src_H', C.c_int * 2), ('src_W', C.c_int * 2), ('src_C', C.c_int * 2)]
 
 
 _lib = None

@@ -254,6 +254,7 @@ class FusedBlock:
             a.src[i] = s.data.data_ptr()
             a.src_Cp[i], a.src_Hpitch[i], a.src_Wpitch[i] = s.Cp, s.data.shape[2], s.data.shape[3]
             a.src_H[i], a.src_W[i] = s.H, s.W
+            a.src_C[i] = s.C
         a.H, a.W, a.pad_top, a.pad_left = H, W, pad_top, pad_left
         a.Cout2, a.kh, a.kw, a.sh, a.sw, a.ph, a.pw, a.Ho, a.Wo = (self.cout2, self.kh, self.kw, self.sh,
                                                                     self.sw, self.ph, self.pw, Ho, Wo)

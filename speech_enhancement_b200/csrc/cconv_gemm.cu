@@ -48,6 +48,7 @@ struct GemmParams {
   GTap taps[kMaxTaps];
   int ncls, row_mul, col_mul;
   int kblocks[2], kcol0[2];
+  int klast[2];               // descriptor units (16 B = 8 bf16) of real channels in the LAST k-block of a source: 2, 4, 6 or 8
   int TH, TW, nacc;
   int concat, acc_cols;       // concat: a_hi x [b_hi|b_lo] in one MMA (npad <= 128), 2*npad TMEM columns per accumulator
   int nsplit, unit_rows;      // split mode: every hi / lo slab travels as nsplit column slices of unit_rows rows
@@ -304,6 +305,8 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
           const GGroup G = p.groups[g];
           const int nkb = p.kblocks[G.src];
           for (int kbi = 0; kbi < nkb; ++kbi) {
+            // k-steps of 16 channels; the pad channels at the end of a source are zeros on both operands: skipped
+            const uint32_t kend = kbi == nkb - 1 ? (uint32_t)p.klast[G.src] : 8u;
             timed_wait(&a_full[sa], pa, prof, w_a);
             ptx::tc_fence_after();
             const uint32_t a_base32 = a_ring32 + sa * a_slot16;
@@ -321,8 +324,10 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
                   ptx::umma_bf16_lo32(d, al, b32, idesc1, 1);
 #pragma unroll
                   for (uint32_t k = 2; k < 8; k += 2) {     // 16 bf16 = 32 B = 2 descriptor units
-                    ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc2, 1);
-                    ptx::umma_bf16_lo32(d, al + k, b32 + k, idesc1, 1);
+                    if (k < kend) {
+                      ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc2, 1);
+                      ptx::umma_bf16_lo32(d, al + k, b32 + k, idesc1, 1);
+                    }
                   }
                 }
                 ptx::umma_commit(&b_empty[sb]);
@@ -340,8 +345,10 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
                     ptx::umma_bf16_lo32(d, ah, b32, idesc1, 1);
 #pragma unroll
                     for (uint32_t k = 2; k < 8; k += 2) {
-                      ptx::umma_bf16_lo32(d, al + k, b32 + k, idesc1, 1);
-                      ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc1, 1);
+                      if (k < kend) {
+                        ptx::umma_bf16_lo32(d, al + k, b32 + k, idesc1, 1);
+                        ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc1, 1);
+                      }
                     }
                   }
                   ptx::umma_commit(&b_empty[sb]);
@@ -355,7 +362,8 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
                   uint32_t ah = a_tap32, d = tmem_buf + (uint32_t)nh * unit_rows;
                   for (uint32_t a = 0; a < nacc; ++a, ah += sub16, d += acc_cols) {
 #pragma unroll
-                    for (uint32_t k = 0; k < 8; k += 2) ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc1, 1);
+                    for (uint32_t k = 0; k < 8; k += 2)
+                      if (k < kend) ptx::umma_bf16_lo32(d, ah + k, b32 + k, idesc1, 1);
                   }
                   ptx::umma_commit(&b_empty[sb]);
                   if (++sb == SB) { sb = 0; pb ^= 1u; }
@@ -763,6 +771,14 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
               reinterpret_cast<uintptr_t>(p.y) % 16 == 0) ? 1 : 0;
   p.kblocks[0] = a->src_Cp[0] / 64; p.kcol0[0] = 0;
   p.kblocks[1] = a->nsrc == 2 ? a->src_Cp[1] / 64 : 0; p.kcol0[1] = a->src_Cp[0];
+  for (int i = 0; i < 2; ++i) {
+    // real channels of source i (0 = unknown: every channel of the pitch): pad channels are zero in the activations
+    // AND in the prepared weights, so whole 16-channel k-steps of padding are not issued
+    const int Cp = i < a->nsrc ? a->src_Cp[i] : 0, Cr = i < a->nsrc ? a->src_C[i] : 0;
+    int last = 64;
+    if (Cr > 0 && Cr <= Cp && Cr > Cp - 64) last = Cr - (Cp - 64);
+    p.klast[i] = 2 * ((last + 15) / 16);
+  }
   int64_t ntiles = 0;
   for (int ci = 0; ci < p.ncls; ++ci) {
     GClass& c = p.cls[ci];
