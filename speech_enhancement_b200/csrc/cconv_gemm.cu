@@ -61,7 +61,7 @@ struct GemmParams {
   __nv_bfloat16* y_cl2;
   int64_t y_bs, y_cs, y_hs, y_ws, y_off, y_lim;   // fp32 output addressing (defaults = NCHW)
   const float* y_scale;                           // optional per-position scale (iSTFT normaliser)
-  int y_vec4;                                     // fp32 output rows are channel-contiguous and 16-byte aligned
+  int y_vec4;                                     // fp32 output rows are channel-contiguous and 16-byte (1) / 32-byte (2) aligned
   unsigned long long* prof;                       // SE_GEMM_PROF=1: per-role wait/work cycle counters (tuning aid)
 };
 
@@ -455,7 +455,17 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
           }
           if (do_f32 && c0 < p.Cout2) {
             const int nv = p.Cout2 - c0;                      // valid columns in this chunk (may exceed 32)
-            if (p.y_vec4) {
+            if (p.y_vec4 == 2) {
+              // 256-bit stores: a whole 32-byte sector per lane and instruction (lanes are a row apart)
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (8 * j + 7 < nv) {
+                  uint32_t w[8];
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) w[i] = __float_as_uint(v[8 * j + i]);
+                  ptx::st_global_v8(yb + c0 + 8 * j, w);
+                }
+            } else if (p.y_vec4) {
               float4* y4 = reinterpret_cast<float4*>(yb + c0);
 #pragma unroll
               for (int j = 0; j < 8; ++j)
@@ -769,6 +779,9 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   p.y_vec4 = (p.y != nullptr && p.y_cs == 1 && p.y_lim == 0 && p.y_scale == nullptr && a->Cout2 % 4 == 0 &&
               p.y_bs % 4 == 0 && p.y_hs % 4 == 0 && p.y_ws % 4 == 0 && p.y_off % 4 == 0 &&
               reinterpret_cast<uintptr_t>(p.y) % 16 == 0) ? 1 : 0;
+  if (p.y_vec4 && a->Cout2 % 8 == 0 && p.y_bs % 8 == 0 && p.y_hs % 8 == 0 && p.y_ws % 8 == 0 && p.y_off % 8 == 0 &&
+      reinterpret_cast<uintptr_t>(p.y) % 32 == 0)
+    p.y_vec4 = 2;
   p.kblocks[0] = a->src_Cp[0] / 64; p.kcol0[0] = 0;
   p.kblocks[1] = a->nsrc == 2 ? a->src_Cp[1] / 64 : 0; p.kcol0[1] = a->src_Cp[0];
   for (int i = 0; i < 2; ++i) {
