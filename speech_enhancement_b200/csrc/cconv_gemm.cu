@@ -658,6 +658,10 @@ constexpr double kFillLatency = 2500.0;          // request -> data landed (cycl
 static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int span_max, int npad) {
   TileChoice best{0, 0, 0, 0, 0, 0, 1, 1e300};
   const int nsm = num_sms();
+  static const char* ovh_env = getenv("SE_GEMM_TILE_OVH");   // tuning aid: fixed cycles per tile in the cost model
+  // measured with SE_GEMM_PROF on the short-K layers: ~2-2.8 kcycles per tile that no MMA covers (DCUNet 7x1: 800 -> 2500
+  // moves the plan from 4x32 / 1 accumulator to 8x16 / 2 accumulators, 1.98 -> 1.56 ms)
+  const double tile_ovh = ovh_env ? atof(ovh_env) : 2500.0;
   for (int mode = 0; mode < 3; ++mode) {
     // mode 0: concat (a_hi x [b_hi|b_lo], a_lo x b_hi); 1: split hi / lo; 2: split + two column slices
     const bool concat = mode == 0;
@@ -705,7 +709,7 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
           const int buf_cols = round_up(nacc * acc_cols, 32);
           const bool two_bufs = buf_cols + tm_need <= 512;
           const double epi = acc_avg * (180.0 * npad + 1500.0);
-          per_tile = two_bufs ? fmax(per_tile, epi) + 800.0 : per_tile + epi + 800.0;
+          per_tile = two_bufs ? fmax(per_tile, epi) + tile_ovh : per_tile + epi + tile_ovh;
           total += per_tile * n;
           tiles += n;
         }
