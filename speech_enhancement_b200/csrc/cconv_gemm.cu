@@ -651,7 +651,16 @@ struct TileChoice { int TH, TW, nacc, SA, SB, concat, nsplit; double cost; };
 
 // MMA cost model measured with scripts/mma_rate.cu (cta_group::1, SS operands, 128B swizzle):
 //   cycles(128 x N x 16) = max(N / 2, ~84)
-static inline double mma_cycles(int n) { return fmax(n / 2.0, 84.0); }
+// cycles of one 128 x n x 16 bf16 MMA.  model 0: max(n / 2, 84) (scripts/mma_rate.cu, MMAs alone on the SM);
+// model 1: what the issuing thread sees inside the pipeline (SE_GEMM_PROF: 135 at n = 256, 90 at 128, ~75 at <= 64)
+static inline double mma_cycles(int n) {
+  static const char* env = getenv("SE_GEMM_MMA_MODEL");
+  static const int model = env ? atoi(env) : 0;
+  if (model == 0) return fmax(n / 2.0, 84.0);
+  if (n <= 64) return 75.0;
+  if (n <= 128) return 75.0 + (n - 64) * (15.0 / 64.0);
+  return 90.0 + (n - 128) * (45.0 / 128.0);
+}
 constexpr double kFillBytesPerCycle = 36.0;      // sustained L2 -> SMEM fill per SM
 constexpr double kFillLatency = 2500.0;          // request -> data landed (cycles), covers one B unit
 
@@ -661,6 +670,16 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
   static const char* ovh_env = getenv("SE_GEMM_TILE_OVH");   // tuning aid: fixed cycles per tile in the cost model
   // measured with SE_GEMM_PROF on the short-K layers: ~2-2.8 kcycles per tile that no MMA covers (DCUNet 7x1: 800 -> 2500
   // moves the plan from 4x32 / 1 accumulator to 8x16 / 2 accumulators, 1.98 -> 1.56 ms)
+  static const char* epi_env = getenv("SE_GEMM_EPI_COL");    // tuning aid: epilogue cycles per accumulator column
+  // measured (SE_GEMM_PROF, 8 epilogue warps, 256-bit stores): 41-52 cycles per accumulator column
+  const double epi_col = epi_env ? atof(epi_env) : 50.0;
+  // Split mode under-delivers against this model wherever the concat form exists (three 128-row operand reads per
+  // k-step instead of two, two B units per tap in a 4-5 slot ring).  Forced-plan sweeps (SE_GEMM_FORCE) over DCCRN,
+  // DCUNet and FRCRN put the concat form ahead on every N = 128 layer, by 6-20 %; penalties of 1.15 / 1.3 / 1.6 gave
+  // DCUNet conv stacks of 30.3 / 29.9 / 29.6 ms (31.3 with none) and FRCRN 19.0 / 18.8 / 17.9 ms (18.8): at 1.6 the
+  // planner takes the concat form whenever npad <= 128.
+  static const char* pen_env = getenv("SE_GEMM_SPLIT_PENALTY");
+  const double split_penalty = pen_env ? atof(pen_env) : 1.6;
   const double tile_ovh = ovh_env ? atof(ovh_env) : 2500.0;
   for (int mode = 0; mode < 3; ++mode) {
     // mode 0: concat (a_hi x [b_hi|b_lo], a_lo x b_hi); 1: split hi / lo; 2: split + two column slices
@@ -708,7 +727,7 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
           // it hides behind the next tile's MMAs only with two TMEM buffers
           const int buf_cols = round_up(nacc * acc_cols, 32);
           const bool two_bufs = buf_cols + tm_need <= 512;
-          const double epi = acc_avg * (180.0 * npad + 1500.0);
+          const double epi = acc_avg * (epi_col * npad + 1500.0);
           per_tile = two_bufs ? fmax(per_tile, epi) + tile_ovh : per_tile + epi + tile_ovh;
           total += per_tile * n;
           tiles += n;
@@ -716,6 +735,7 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
         const double waves = ceil((double)tiles / nsm);
         double cost = total / (double)tiles * waves;                 // ~cycles, 1 CTA per SM
         if (TW < 32) cost *= 1.0 + 0.03 * (32 / TW);                 // narrow rows: poorly coalesced epilogue
+        if (!concat && npad <= 128) cost *= split_penalty;
         if (cost < best.cost) best = TileChoice{TH, TW, nacc, SA, SB, concat ? 1 : 0, nsplit, cost};
       }
     }
