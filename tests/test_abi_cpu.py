@@ -1,6 +1,7 @@
 """CPU-side checks of the C-ABI boundary: the library loads without a GPU driver, exports every
 symbol include/se_b200.h declares, and argument validation fails loudly (no compute calls)."""
 import ctypes as C
+import os
 
 import pytest
 import torch
@@ -63,3 +64,26 @@ def test_init_kernels_matches_oracle():
             kr, wr = oracle.init_kernels_ref(win, fft, inverse=inv)
             assert k.shape == (fft + 2, 1, win) and w.shape == (1, win, 1)
             assert (k - kr).abs().max() < 2e-7 and torch.equal(w, wr)
+
+
+def test_conv_args_mirror_matches_the_c_struct(tmp_path):
+    """the ctypes mirror of `se_cconv_args` has the C struct's size and field offsets (compiled from include/se_b200.h
+    with the host C compiler: the header is plain C)"""
+    import ctypes as C
+    import shutil
+    import subprocess
+    from speech_enhancement_b200 import _abi
+    cc = shutil.which('gcc') or shutil.which('cc')
+    if cc is None:
+        pytest.skip('no host C compiler')
+    fields = [name for name, _ in _abi.ConvArgs._fields_]
+    src = tmp_path / 'layout.c'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "se_b200.h"\nint main(void) {\n'
+                   '  printf("%zu\\n", sizeof(se_cconv_args));\n' +
+                   ''.join(f'  printf("%zu\\n", offsetof(se_cconv_args, {f}));\n' for f in fields) +
+                   '  return 0;\n}\n')
+    exe = tmp_path / 'layout'
+    subprocess.run([cc, '-I', os.path.dirname(_abi.HEADER_PATH), str(src), '-o', str(exe)], check=True)
+    out = [int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    assert out[0] == C.sizeof(_abi.ConvArgs)
+    assert out[1:] == [getattr(_abi.ConvArgs, f).offset for f in fields]
