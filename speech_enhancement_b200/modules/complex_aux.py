@@ -149,7 +149,12 @@ class ComplexLSTM(nn.Module):
             by_real, by_imag = lstm_pair_forward(self, [self.real_lstm, self.imag_lstm], [real, imag], self.proj_engine)
             r2r, i2r = torch.chunk(by_real, 2, dim=0)
             r2i, i2i = torch.chunk(by_imag, 2, dim=0)
-            return merge_real_imag(x, r2r - i2i, r2i + i2r, dim=-1)
+            # [real | imag] written straight into the halves of the output (complex_nn.py:142-145 without the cat copy)
+            hid = r2r.shape[-1]
+            out = torch.empty(r2r.shape[:-1] + (2 * hid,), device=x.device, dtype=r2r.dtype)
+            torch.sub(r2r, i2i, out=out[..., :hid])
+            torch.add(r2i, i2r, out=out[..., hid:])
+            return out
         both = torch.cat([real, imag], dim=bdim)
         if self.rec_kernel and _lstm_rec_ok(self.real_lstm, both):
             bf = self.real_lstm.batch_first
