@@ -46,3 +46,25 @@ def test_reference_models_bind_to_this_package():
     code = CODE % (ROOT, REF, os.path.join(ROOT, 'tests', 'golden', 'models.npz'))
     res = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=300)
     assert res.returncode == 0 and 'dropin ok' in res.stdout, res.stdout[-2000:] + res.stderr[-4000:]
+
+
+def test_phase_folded_transposed_conv_prototype_matches_torch():
+    """scripts/phase_fold_prototype.py (the planned N-folding of the stride-2 decoder layers) reproduces
+    F.conv_transpose2d for the DCCRN and DCUNet decoder geometries"""
+    import importlib.util
+    import os
+    import torch
+    import torch.nn.functional as F
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'scripts', 'phase_fold_prototype.py')
+    spec = importlib.util.spec_from_file_location('phase_fold_prototype', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    g = torch.Generator().manual_seed(5)
+    for k, st, pd, op, groups in [((5, 2), (2, 1), (2, 0), (1, 0), 6), ((7, 5), (2, 2), (3, 2), (0, 0), 12),
+                                  ((5, 3), (2, 1), (2, 1), (0, 0), 9)]:
+        x = torch.randn(2, 6, 5, 7, dtype=torch.float64, generator=g)
+        w = torch.randn(6, 4, *k, dtype=torch.float64, generator=g)
+        want = F.conv_transpose2d(x, w, stride=st, padding=pd, output_padding=op)
+        got, n = mod.conv_transpose_folded(x, w, st, pd, op)
+        assert n == groups and got.shape == want.shape
+        assert (got - want).abs().max().item() < 1e-12
