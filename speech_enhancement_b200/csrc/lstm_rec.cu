@@ -6,10 +6,15 @@
 // GEMM by the caller, and this kernel walks the T steps of a few batch rows entirely on one SM:
 //   gates = P[n,t] + W_hh h_{t-1};  i,f,o = sigmoid, g = tanh (gate order i|f|g|o, torch.nn.LSTM);
 //   c_t = f c_{t-1} + i g;  h_t = o tanh(c_t)
-// Batch rows never interact, so there is no inter-CTA synchronisation at all: one thread per gate
-// column (4H = 512 threads for H = 128) keeps its W_hh row on chip for the whole sequence -- KR
-// values in registers, the other H-KR in shared memory, column-major so a warp reads consecutive
-// words -- and h_{t-1} is broadcast from shared memory.  Two __syncthreads per step.
+// Batch rows never interact, so there is no inter-CTA synchronisation at all.  Three kernels:
+//   lstm_rec_kernel          one thread per gate column (4H threads) keeps its W_hh row on chip for the whole
+//                            sequence -- KR values in registers, the other H-KR in shared memory, column-major so a
+//                            warp reads consecutive words -- h_{t-1} broadcast from shared memory, two
+//                            __syncthreads per step.  Used for H = 64.
+//   lstm_rec2_kernel         two gate columns per thread, the four gates of a unit in one warp, one barrier per
+//                            step: the production kernel for H = 128 at more than 74 row jobs.
+//   lstm_rec_cluster_kernel  2-CTA cluster, all of W_hh in registers, h halves exchanged through DSMEM: H = 128 with
+//                            at most (#SMs / 2) row jobs.
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
