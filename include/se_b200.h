@@ -116,6 +116,21 @@ SE_API int se_cconvT2d_fwd(const float* x, const float* packed, const float* bia
 SE_API int64_t se_cconv_workspace_bytes(int64_t B, int Cin2, int H, int W, int Cout2, int kh, int kw,
                                  int sh, int sw, int transposed);
 
+/* ---- allocation-free variant of se_cconv2d_fwd ---------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, layouts and result as se_cconv2d_fwd(engine = SE_ENGINE_UMMA) without the workspace
+ * pair: the CL2 input + bf16 weight staging lives in a file-scope `static __device__` array of
+ * SE_STATIC_WS_BYTES inside the library (every device that loads the library holds it until exit).
+ * The call allocates and frees nothing.  Problems whose se_cconv_workspace_bytes() exceeds
+ * SE_STATIC_WS_BYTES are rejected with SE_ERR_WORKSPACE; shapes outside the tensor engine
+ * (Cin2 < 16, Cout2 > 256, kh*kw > 49) with SE_ERR_UNSUPPORTED.  All calls on a device share the one
+ * array: calls that may overlap on the GPU (different streams or host threads) race -- serialise them. */
+#define SE_STATIC_WS_BYTES (32 * 1024 * 1024)
+SE_API int se_cconv2d_fwd_static(const float* x, const float* packed, const float* bias_packed_or_null,
+                          int64_t B, int Cin2, int H, int W, int Cout2, int kh, int kw,
+                          int sh, int sw, int ph, int pw, float* y, int Ho, int Wo, void* stream);
+
 /* ---- tcgen05 conv engine, chainable form ------------------------------------------------------
  * Activations travel between layers in "CL2": channels-last bf16 hi|lo planes [B][2][H][W][Cp]
  * (value = hi + lo, Cp = channels padded to a multiple of 64, pad channels zero).

@@ -32,6 +32,7 @@ _SIGS = {
     'se_cconv_pack_weight': (C.c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P]),
     'se_cconv2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
     'se_cconvT2d_fwd': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _I, _P, _L, _P]),
+    'se_cconv2d_fwd_static': (C.c_int, [_P, _P, _P, _L] + [_I] * 10 + [_P, _I, _I, _P]),
     'se_cconv_workspace_bytes': (C.c_int64, [_L] + [_I] * 9),
     'se_cl2_from_nchw': (C.c_int, [_P, _L, _I, _I, _I, _P, _I, _P]),
     'se_cl2_from_strided': (C.c_int, [_P, _L, _L, _L, _L, _I, _I, _I, _P, _I, _P]),

@@ -1092,3 +1092,60 @@ extern "C" int se_cconv_prep_weight(const float* packed, int Cout2, int Cin2, in
       packed, chan_map, reinterpret_cast<__nv_bfloat16*>(wq), Cout2, Cin2, taps, npad, Cp_total);
   return se::check_launch("se_cconv_prep_weight");
 }
+
+// ---- allocation-free variant of se_cconv2d_fwd (no counterpart in the reference; see include/se_b200.h) ----
+// The tensor engine's module path stages the input as CL2 and the weight as bf16 hi|lo slabs in scratch memory.
+// Here that scratch is a file-scope device array instead of a caller-provided workspace, so that callers which
+// may not allocate (CUDA-graph capture, serving loops) have an entry that never calls cudaMalloc / cudaFree.
+// `g_static_ws` below is, in HOST code, only a handle for the symbol: the device address is looked up once per
+// device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels receive.
+// Both staging kernels overwrite every byte the GEMM later reads (pad channels included), so nothing has to be
+// cleared between calls; calls that overlap on the GPU (two streams, two threads) share the array and race.
+static __device__ __align__(256) unsigned char g_static_ws[SE_STATIC_WS_BYTES];
+
+namespace se {
+static int static_ws_ptr(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::atomic<void*> ptrs[kMaxDev];
+  int dev = -1;
+  SE_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) return fail(SE_ERR_UNSUPPORTED, "se_cconv2d_fwd_static: device ordinal %d >= %d", dev, kMaxDev);
+  void* p = ptrs[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    SE_CUDA(cudaGetSymbolAddress(&p, g_static_ws));      // same value from every thread: a benign race
+    if (p == nullptr) return fail(SE_ERR_CUDA, "se_cconv2d_fwd_static: cudaGetSymbolAddress returned NULL");
+    ptrs[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return SE_OK;
+}
+}  // namespace se
+
+extern "C" int se_cconv2d_fwd_static(const float* x, const float* packed, const float* bias, int64_t B, int Cin2,
+                                     int H, int W, int Cout2, int kh, int kw, int sh, int sw, int ph, int pw,
+                                     float* y, int Ho, int Wo, void* stream) {
+  const char* nm = "se_cconv2d_fwd_static";
+  SE_REQUIRE(x && packed && y, "%s: null pointer", nm);
+  SE_REQUIRE(B >= 0 && Cin2 > 0 && Cout2 > 0 && (Cin2 % 2) == 0 && (Cout2 % 2) == 0,
+             "%s: channel counts must be positive and even", nm);
+  SE_REQUIRE(H > 0 && W > 0 && kh > 0 && kw > 0 && sh > 0 && sw > 0 && ph >= 0 && pw >= 0 && Ho > 0 && Wo > 0,
+             "%s: bad geometry", nm);
+  SE_REQUIRE(Ho == (H + 2 * ph - kh) / sh + 1 && Wo == (W + 2 * pw - kw) / sw + 1,
+             "%s: output size does not match geometry", nm);
+  if (B == 0) return SE_OK;
+  se::ConvGeom g{Cin2, H, W, Cout2, kh, kw, sh, sw, ph, pw, Ho, Wo};
+  if (!se::cconv_umma_supported(false, B, g))
+    return se::fail(SE_ERR_UNSUPPORTED, "%s: shape outside the tensor engine (Cin2 >= 16, Cout2 <= 256, taps <= %d)", nm,
+                    se::kMaxTaps);
+  const int64_t need = se::cconv_umma_workspace_bytes(false, B, Cin2, H, W, Cout2, kh, kw, sh, sw);
+  if (need > (int64_t)SE_STATIC_WS_BYTES)
+    return se::fail(SE_ERR_WORKSPACE, "%s: this problem needs %lld bytes of scratch, the static array holds %lld "
+                    "(SE_STATIC_WS_BYTES); use se_cconv2d_fwd with a caller-provided workspace", nm, (long long)need,
+                    (long long)SE_STATIC_WS_BYTES);
+  const char* prof = getenv("SE_GEMM_PROF");              // the profiling aid allocates a counter buffer
+  if (prof && atoi(prof) != 0) return se::fail(SE_ERR_UNSUPPORTED, "%s: unset SE_GEMM_PROF (it allocates)", nm);
+  void* ws = nullptr;
+  int rc = se::static_ws_ptr(&ws);
+  if (rc != SE_OK) return rc;
+  return se::cconv_fwd_umma(false, x, packed, bias, B, g, y, ws, (int64_t)SE_STATIC_WS_BYTES, (cudaStream_t)stream);
+}
