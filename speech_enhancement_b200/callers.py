@@ -279,6 +279,11 @@ class DCUNet(nn.Module):
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)                                               # [B, 2F, T]
         B, C2, T = spec.shape
+        if self.normalize:
+            # dcunet.py:127-130 on the [B, 2F, T] view (same element set as [B, 2, F, T] over dims 1-3); the mask is
+            # applied to the NORMALISED spectrum (`identity`, :134), so `spec` is simply replaced
+            mean, std = spec.mean(dim=(1, 2), keepdim=True), spec.std(dim=(1, 2), keepdim=True)
+            spec = (spec - mean) / (std + 1e-8)
         first, enc, dec = self._fused_blocks()
         act, _ = first.first_layer(spec, C2 * T, n_bins * T, T, B, n_bins, T)
         skips = []
@@ -299,7 +304,7 @@ class DCUNet(nn.Module):
         return est_spec, torch.clamp_(wav, -1, 1)
 
     def forward(self, x):
-        if not self.normalize and _fusable(self, x, self.first_conv):
+        if _fusable(self, x, self.first_conv):
             return self._forward_fused(x)
         n_bins = self.fft_size // 2 + 1
         spec = self.stft(x)

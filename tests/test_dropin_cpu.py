@@ -48,6 +48,38 @@ def test_reference_models_bind_to_this_package():
     assert res.returncode == 0 and 'dropin ok' in res.stdout, res.stdout[-2000:] + res.stderr[-4000:]
 
 
+def test_accelerate_recognises_reference_instances_and_refuses_others():
+    """dropin.accelerate() on instances of the staged reference classes (oracle/_ref): structure check on the CPU,
+    and the loud fallback to the reference's own forward for a CPU input"""
+    import warnings
+    import torch
+    from oracle import ref_loader
+    from speech_enhancement_b200 import dropin
+    if not ref_loader.available():
+        pytest.skip(ref_loader.why_unavailable())
+    orig, drop = ref_loader.load_original(), ref_loader.load_dropin()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        for cls, args in (('DCCRN', ('dccrn-CL', 400, 100, 512)), ('DCUNet', ('dcunet10', 512, 128, 512)),
+                          ('FRCRN', (320, 160, 640))):
+            m = getattr(drop, cls)(*args).eval()
+            assert dropin.accelerate(m) is m and m._se_chained is not None
+            assert dropin.accelerate(m) is m                            # idempotent
+            dropin.decelerate(m)
+            assert 'forward' not in m.__dict__
+        with pytest.raises(RuntimeError, match='no chained forward'):
+            dropin.accelerate(drop.CARN(320, 160, 512))
+        with pytest.raises(RuntimeError, match='not this package'):     # the reference bound to its OWN modules
+            dropin.accelerate(orig.DCCRN('dccrn-CL', 400, 100, 512))
+        with pytest.raises(RuntimeError, match='is_complex=False'):
+            dropin.accelerate(drop.DCCRN('dccrn-CL', 400, 100, 512, is_complex=False))
+    # the original binding still runs on the CPU next to the drop-in binding (one process, two bindings)
+    with torch.no_grad(), warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        wav = orig.DCCRN('dccrn-CL', 400, 100, 512).eval()(torch.zeros(1, 4000))[1]
+    assert wav.shape == (1, 3988)
+
+
 def test_phase_folded_transposed_conv_prototype_matches_torch():
     """scripts/phase_fold_prototype.py (the planned N-folding of the stride-2 decoder layers) reproduces
     F.conv_transpose2d for the DCCRN and DCUNet decoder geometries"""
