@@ -1,21 +1,30 @@
 #!/usr/bin/env python
 """bench.py -- DCCRN-CL enhancement throughput (audio-seconds enhanced per second) on B200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference] [--model M]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A "step" is one forward of DCCRN-CL (400/100/512, _2008_00264_dccrn.py:124) over a batch of
-`--batch` synthetic 4 s / 16 kHz noisy utterances PER GPU (utterance-sharded, weak scaling, no
-collective on the data path).  Rank 0 prints ONE JSON line (contract in the task statement):
-  value     audio-s/s with inputs resident in HBM (CUDA events, max over ranks)
-  e2e       same metric through the public API from pinned HOST buffers: H2D of the batch and
-            D2H of the enhanced waveform inside the timed region
-  roofline  the complex-conv stack (dominant kernels): algorithmic FLOPs (SURVEY.md 8a,
-            65.95 GFLOP/utt) / summed CUDA-event time of the conv launches, vs MEASURED_PEAKS.json
-  stages    per-stage device time + HBM GB/s of STFT / iSTFT / mask against the measured copy peak
-  cpu_baseline  the CPU oracle (torch fp32 restatement of the reference path) timed on this box
-`--impl reference` times that CPU oracle alone (the reference is pure Python and cannot travel to
-the GPU box) on all host threads, same metric/unit/config.
+A "step" is one forward of DCCRN-CL (400/100/512, _2008_00264_dccrn.py:124) over a batch of `--batch`
+synthetic 4 s / 16 kHz noisy utterances PER GPU (utterance-sharded, weak scaling, no collective on the data
+path).  Rank 0 prints ONE JSON line (contract in the task statement):
+  value         audio-s/s with inputs resident in HBM (CUDA events, max over ranks)
+  e2e           same metric through the public API from pinned HOST buffers: H2D of the batch and D2H of the
+                enhanced waveform inside the timed region
+  roofline      the complex-conv stack (dominant kernels): algorithmic FLOPs (SURVEY.md 8a, 65.95 GFLOP/utt) /
+                summed CUDA-event time of the conv launches, vs MEASURED_PEAKS.json
+  stages        per-stage device time + HBM GB/s of STFT / iSTFT / mask against the measured copy peak
+  parity        utterances {0, B/2, B-1} of a bench batch against (a) the same utterances run alone on the GPU
+                and (b) the CPU arm; the process exits non-zero when the north-star bar (rel-L2 1e-3, SI-SNR
+                0.01 dB) is missed
+  cpu_baseline  the reference's own fp32 PyTorch path on this box's host cores (kind "reference": the unmodified
+                model class staged in oracle/_ref; kind "port" when that directory is absent)
+  other_configs the other BASELINE.json configurations in compact form (same protocol): DCCRN-CL at batch 1
+                (latency, eager and CUDA-graph replay), DCUNet-20 64 x 4 s, FRCRN 128 x 4 s over the GPUs of
+                the run, CARN training step global batch 32 over the GPUs of the run
+The model timed on the GPU is the reference's own class (oracle/_ref, unmodified) bound to this package by
+dropin.install() + dropin.accelerate() when oracle/_ref is staged, else the package's host model
+(speech_enhancement_b200.callers); `config.gpu_model` says which.
+`--impl reference` times the CPU arm alone on all host threads, same metric / unit / config.
 """
 import argparse
 import json
@@ -24,6 +33,7 @@ import subprocess
 import sys
 import threading
 import time
+import warnings
 
 import torch
 
@@ -33,8 +43,9 @@ sys.path.insert(0, ROOT)
 SR, CLIP_S = 16000, 4
 L = SR * CLIP_S
 UNIT = 'audio-s/s'
-# BASELINE.json's metric is quoted on DCCRN (default); the two other complex families of configs[1] / [2]
-# run through the same bench with --model.  conv GFLOP/utt: SURVEY.md 8a/8d (sum of 2*M*K*N per layer).
+TOL_REL_L2, TOL_SISNR_DB = 1e-3, 0.01          # north-star bar
+# BASELINE.json's metric is quoted on DCCRN (default); the other complex families of configs[1] / [2] run through
+# the same code with --model.  conv GFLOP/utt: SURVEY.md 8a/8d (sum of 2*M*K*N per layer).
 MODELS = {
     'dccrn': dict(cls='DCCRN', args=('dccrn-CL', 400, 100, 512), stft=(400, 100, 512), conv_gflop=65.95,
                   name='DCCRN-CL', metric='dccrn_cl_audio_seconds_enhanced_per_second', act_mb=268),
@@ -42,12 +53,11 @@ MODELS = {
                      name='DCUNet-20', metric='dcunet20_audio_seconds_enhanced_per_second', act_mb=600),
     'frcrn': dict(cls='FRCRN', args=(320, 160, 640), stft=(320, 160, 640), conv_gflop=97.61,
                   name='FRCRN', metric='frcrn_audio_seconds_enhanced_per_second', act_mb=500),
+    # BASELINE configs[3]: CARN forward+backward+AdamW, GLOBAL batch 32 split over the GPUs (strong scaling),
+    # gradient allreduce over NCCL (speech_enhancement_b200/training.py)
+    'carn_train': dict(cls='CARN', args=(320, 160, 512), stft=(320, 160, 512), conv_gflop=0.0, train=True,
+                       name='CARN training step', metric='carn_train_audio_seconds_per_second', act_mb=0),
 }
-# BASELINE configs[3]: CARN forward+backward+AdamW, GLOBAL batch 32 split over the GPUs (strong scaling),
-# one flat-gradient allreduce per step (speech_enhancement_b200/training.py)
-MODELS['carn_train'] = dict(cls='CARN', args=(320, 160, 512), stft=(320, 160, 512), conv_gflop=0.0, train=True,
-                            name='CARN training step', metric='carn_train_audio_seconds_per_second', act_mb=0)
-MODEL = MODELS['dccrn']
 
 
 def peaks():
@@ -57,7 +67,23 @@ def peaks():
         return {'hbm_gbs': p['hbm_gbs'], 'bf16_tflops': p['bf16_tflops'],
                 'bf16_tflops_sustained': p.get('bf16_tflops_sustained', p['bf16_tflops']), 'source': 'measured'}
     except Exception:
+        # B200_PROFILING.md fallback figures (used only when the driver-written file is absent; `peak_source` says so)
         return {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0, 'source': 'fallback'}
+
+
+def conv_traffic(model_key, batch):
+    """measured DRAM traffic of the conv launches of one step: sum of dram__bytes_read + dram__bytes_write over the
+    launches of one `ncu --set full` capture of the CURRENT kernels, committed as profiles/r2_conv_traffic.json by
+    scripts/ncu_layers.py.  None (printed as null) when no capture of this model at this batch is committed."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'r2_conv_traffic.json')) as f:
+            t = json.load(f)
+        e = t[model_key]
+        if int(e['batch']) == int(batch):
+            return float(e['dram_bytes_per_step']), e.get('source', 'profiles/r2_conv_traffic.json')
+    except Exception:
+        pass
+    return None, None
 
 
 class ClockSampler:
@@ -94,32 +120,70 @@ class ClockSampler:
                 'reasons': reasons, 'samples': len(sm)}
 
 
-def build_models(device, seed=0):
+# ------------------------------------------------------------------------------------ models
+def reference_staged():
+    from oracle import ref_loader
+    return ref_loader.available()
+
+
+def build_gpu_model(key, device, seed=0):
+    """(model on `device`, description).  The reference's own class behind dropin when oracle/_ref is staged."""
+    from speech_enhancement_b200 import callers, dropin
+    from speech_enhancement_b200.synth import seeded_state_dict
+    m = MODELS[key]
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        if reference_staged() and not m.get('train'):
+            from oracle import ref_loader
+            model = getattr(ref_loader.load_dropin(), m['cls'])(*m['args'])
+            model.load_state_dict(seeded_state_dict(model, seed=seed))
+            model = dropin.accelerate(model.eval().to(device))
+            return model, ('reference model class (oracle/_ref, unmodified) + dropin.install() + dropin.accelerate(): '
+                           'chained engine behind model.forward')
+        model = getattr(callers, m['cls'])(*m['args'])
+        model.load_state_dict(seeded_state_dict(model, seed=seed))
+    what = 'speech_enhancement_b200.callers.' + m['cls']
+    if m.get('train'):
+        what += ' (STFT / fused mask / iSTFT autograd nodes of this package around stock cuDNN layers)'
+    return model.eval().to(device), what
+
+
+def build_cpu_model(key, seed=0):
+    """(CPU model, kind): the unmodified reference class when staged ("reference"), else the oracle port ("port")."""
     from speech_enhancement_b200 import callers
     from speech_enhancement_b200.synth import seeded_state_dict
-    model = getattr(callers, MODEL['cls'])(*MODEL['args'])
-    model.load_state_dict(seeded_state_dict(model, seed=seed))
-    return model.eval().to(device)
+    m = MODELS[key]
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        if reference_staged():
+            from oracle import ref_loader
+            model, kind = getattr(ref_loader.load_original(), m['cls'])(*m['args']), 'reference'
+        else:
+            from oracle.modules_ref import OPS
+            model, kind = getattr(callers, m['cls'])(*m['args'], ops=OPS), 'port'
+        model.load_state_dict(seeded_state_dict(model, seed=seed))
+    return model.eval(), kind
 
 
-def build_oracle(seed=0):
-    from speech_enhancement_b200 import callers
-    from speech_enhancement_b200.synth import seeded_state_dict
-    from oracle.modules_ref import OPS
-    model = getattr(callers, MODEL['cls'])(*MODEL['args'], ops=OPS)
-    model.load_state_dict(seeded_state_dict(model, seed=seed))
-    return model.eval()
+def host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1)
 
 
-def time_cpu_oracle(batch, iters, warmup=1):
-    """audio-s/s of the CPU oracle on `batch` x 4 s, all host threads; returns (value, cores, seconds/iter)."""
-    from speech_enhancement_b200.synth import synth_noisy_speech
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1)
+def cpu_setup():
+    cores = host_cores()
     torch.set_num_threads(cores)
     torch.set_flush_denormal(True)      # CPU at its best: denormals in the synthetic activations cost 3x otherwise
-    model = build_oracle()
+    return cores
+
+
+def time_cpu_forward(key, batch, iters, warmup=1):
+    """audio-s/s of the CPU arm on `batch` x 4 s, all host threads; returns (value, threads, seconds/iter, kind)."""
+    from speech_enhancement_b200.synth import synth_noisy_speech
+    cpu_setup()
+    model, kind = build_cpu_model(key)
     x = synth_noisy_speech(batch, L, seed=1)
-    with torch.no_grad():
+    with torch.no_grad(), warnings.catch_warnings():
+        warnings.simplefilter('ignore')
         for _ in range(warmup):
             model(x)
         ts = []
@@ -129,39 +193,66 @@ def time_cpu_oracle(batch, iters, warmup=1):
             ts.append(time.perf_counter() - t0)
     ts.sort()
     med = ts[len(ts) // 2]
-    return batch * CLIP_S / med, torch.get_num_threads(), med
+    return batch * CLIP_S / med, torch.get_num_threads(), med, kind
 
 
-def config_dict(batch, n_gpus):
-    win, hop, fft = MODEL['stft']
-    return {'workload': f'{MODEL["name"]} forward (win {win} / hop {hop} / fft {fft}), {batch} x 4 s 16 kHz utterances '
-                        'per GPU, fp32 I/O, eval/no_grad, seeded random-init weights',
-            'per_gpu_batch': batch, 'global_batch': batch * n_gpus, 'clip_seconds': CLIP_S, 'sample_rate': SR,
-            'parallelism': f'utterance-sharded x{n_gpus}, no data-path collective',
-            'l2_policy': f'per-step activation working set (>= {MODEL["act_mb"]} MB/utt) exceeds the 126 MB L2; '
-                         'inputs rotate over 3 buffers'}
+def cpu_kind_text(kind):
+    return ('the reference\'s own model class and modules, unmodified (oracle/_ref), fp32 PyTorch CPU'
+            if kind == 'reference' else 'torch-CPU restatement of the reference path (oracle port)') + ', flush-denormal on'
 
 
+def config_dict(key, batch, n_gpus, gpu_model=None):
+    m = MODELS[key]
+    win, hop, fft = m['stft']
+    d = {'workload': f'{m["name"]} forward (win {win} / hop {hop} / fft {fft}), {batch} x 4 s 16 kHz utterances '
+                     'per GPU, fp32 I/O, eval/no_grad, seeded random-init weights',
+         'per_gpu_batch': batch, 'global_batch': batch * n_gpus, 'clip_seconds': CLIP_S, 'sample_rate': SR,
+         'parallelism': f'utterance-sharded x{n_gpus}, no data-path collective',
+         'l2_policy': f'per-step activation working set (>= {m["act_mb"]} MB/utt) exceeds the 126 MB L2; '
+                      'inputs rotate over 3 buffers'}
+    if gpu_model:
+        d['gpu_model'] = gpu_model
+    return d
+
+
+# ------------------------------------------------------------------------------------ reference arm
 def run_reference(args):
-    rank = int(os.environ.get('RANK', '0'))
-    if rank != 0:
+    """--impl reference: the CPU arm alone (rank 0 only), at batch 1 and batch 8; the line's
+    value is the better of the two."""
+    if int(os.environ.get('RANK', '0')) != 0:
         return
-    batch = min(args.batch, 2)
-    value, cores, _ = time_cpu_oracle(batch, iters=max(args.steps, 1), warmup=max(args.warmup, 1))
-    sec = batch * CLIP_S / value
-    line = {'impl': 'reference', 'metric': MODEL['metric'], 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+    key = args.model
+    m = MODELS[key]
+    if m.get('train'):
+        value, cores, sec, kind = time_cpu_train(4, max(args.steps, 1))
+        line = {'impl': 'reference', 'metric': m['metric'], 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+                'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True,
+                'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                'config': {'workload': 'CARN fwd+bwd+AdamW step', 'global_batch': 32},
+                'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': kind,
+                                 'sample': '4 x 4 s utterances per step; ' + cpu_kind_text(kind)},
+                'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+                'gpu_launches': 0}
+        print(json.dumps(line), flush=True)
+        return
+    iters, warm = max(args.steps, 1), max(args.warmup, 1)
+    v1, cores, s1, kind = time_cpu_forward(key, 1, iters, warm)
+    v8, _, s8, _ = time_cpu_forward(key, 8, max(iters // 2, 2), 1)
+    value, sec, nb = (v8, s8, 8) if v8 >= v1 else (v1, s1, 1)
+    line = {'impl': 'reference', 'metric': m['metric'], 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': config_dict(args.batch, args.gpus),
-            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                             'sample': f'{batch} x 4 s utterances per step (bounded sample of the workload), '
-                                       'CPU oracle = torch-CPU restatement of the reference path, flush-denormal on'},
+            'config': config_dict(key, args.batch, args.gpus),
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': kind,
+                             'batch1': {'value': v1, 'latency_ms': s1 * 1e3}, 'batch8': {'value': v8, 'ms': s8 * 1e3},
+                             'sample': f'{nb} x 4 s utterances per step (bounded sample of the workload; the better of '
+                                       f'batch 1 and batch 8, median over the steps); ' + cpu_kind_text(kind)},
             'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line), flush=True)
 
 
-# ------------------------------------------------------------------------------------ GPU arm
+# ------------------------------------------------------------------------------------ GPU arm helpers
 class StageTimer:
     """CUDA-event timing of the hot-path stages through the package's `_abi.stage` brackets (used in a
     SEPARATE profiling pass after the headline timing, so it never perturbs `value`)."""
@@ -190,14 +281,221 @@ class StageTimer:
         return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self.events.items()}
 
 
+class Dist:
+    """rank / world of this process and the barrier + max-over-ranks timing every number goes through"""
+
+    def __init__(self):
+        self.rank = int(os.environ.get('RANK', '0'))
+        self.world = int(os.environ.get('WORLD_SIZE', '1'))
+        self.local = int(os.environ.get('LOCAL_RANK', '0'))
+        if not torch.cuda.is_available():
+            raise RuntimeError('bench.py: no CUDA device (speech_enhancement_b200 has no CPU path)')
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device('cuda', self.local)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group('nccl', device_id=self.dev)
+
+    def barrier(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(self, fn, steps, after=None):
+        """K steps bracketed by barrier + synchronize; device time via CUDA events; max over ranks."""
+        from speech_enhancement_b200 import sharding
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        if after is not None:
+            after()
+        e1.record()
+        self.barrier()
+        return sharding.reduce_max(e0.elapsed_time(e1), device=self.dev)    # the slowest rank defines the step
+
+    def close(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+def si_snr_db(est, target, eps=1e-8):
+    """losses.py:62-84 (per-utterance SI-SNR in dB, mean over the batch), float64"""
+    n = min(est.shape[1], target.shape[1])
+    est, target = est[:, :n].double(), target[:, :n].double()
+    dot = (est * target).sum(1, keepdim=True)
+    s = dot * target / target.pow(2).sum(1, keepdim=True)
+    return (10 * torch.log10((s.pow(2).sum(1) + eps) / ((est - s).pow(2).sum(1) + eps))).mean().item()
+
+
+def rel_l2(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def parity_check(key, model, x_dev, x_host, clean, cpu_model, cpu_kind):
+    """utterances {0, B/2, B-1} of the bench batch `x_dev`: the batched GPU result against the same utterances run
+    alone (batch 1) on the GPU and against the CPU arm.  DCUNet: bins whose mask sits on the branch cut of the
+    reference's angle / magnitude quirk (_1903_03107_dcunet.py:177) are counted and taken from the CPU result
+    before the waveform comparison (tests/test_gpu_reference_dropin.py explains)."""
+    B = x_dev.shape[0]
+    idx = sorted({0, B // 2, B - 1})
+    with torch.no_grad(), warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        spec_b, wav_b = model(x_dev)
+        spec_b, wav_b = spec_b[idx].clone(), wav_b[idx].clone()
+        singles = [model(x_dev[i:i + 1]) for i in idx]
+        wav_1 = torch.cat([s[1] for s in singles], 0)
+        spec_c, wav_c = cpu_model(x_host[idx])
+    out = {'utterances': idx, 'batch': B, 'vs': cpu_kind,
+           'rel_l2_vs_batch1_gpu': rel_l2(wav_b.cpu(), wav_1.cpu())}
+    wav_cmp = wav_b.cpu()
+    if MODELS[key]['cls'] == 'DCUNet':
+        spec_c_d = spec_c.to(spec_b.device)
+        cut = (spec_b - spec_c_d).abs() > 2e-3 * spec_c_d.abs().max()
+        out['branch_cut_bins'] = int(cut.sum().item())
+        out['branch_cut_frac'] = out['branch_cut_bins'] / cut.numel()
+        if out['branch_cut_bins']:
+            with torch.no_grad():
+                wav_cmp = torch.clamp(model.istft(torch.where(cut, spec_c_d, spec_b).contiguous()), -1, 1).cpu()
+    tgt = clean[idx]
+    out['rel_l2'] = rel_l2(wav_cmp, wav_c)
+    out['si_snr_delta_db'] = abs(si_snr_db(wav_cmp, tgt) - si_snr_db(wav_c, tgt))
+    out['ok'] = bool(out['rel_l2'] <= TOL_REL_L2 and out['si_snr_delta_db'] <= TOL_SISNR_DB
+                     and out['rel_l2_vs_batch1_gpu'] <= TOL_REL_L2 and out.get('branch_cut_frac', 0.0) <= 1e-4)
+    out['tolerance'] = {'rel_l2': TOL_REL_L2, 'si_snr_delta_db': TOL_SISNR_DB}
+    return out
+
+
+def bench_inference(key, B, steps, warmup, D, full=True, with_graph=False):
+    """one inference configuration on every rank; rank 0 gets the result dict (other ranks None)."""
+    from speech_enhancement_b200 import _abi
+    from speech_enhancement_b200.pipeline import HostPipeline
+    from speech_enhancement_b200.synth import synth_noisy_speech
+    m = MODELS[key]
+    lib = _abi.lib()
+    dev = D.dev
+    model, gpu_what = build_gpu_model(key, dev)
+    pairs = [synth_noisy_speech(B, L, seed=100 + 7 * D.rank + i, return_clean=True) for i in range(3)]
+    host = [p[0].pin_memory() for p in pairs]
+    dev_in = [h.to(dev) for h in host]
+
+    def step(i):
+        with torch.no_grad():
+            return model(dev_in[i % 3])[1]
+
+    for i in range(max(warmup, 3)):
+        step(i)
+    sampler = ClockSampler(D.local)
+    if D.rank == 0 and full:
+        sampler.start()
+    n0 = lib.se_launch_count()
+    ms = D.timed(step, steps)
+    launches = lib.se_launch_count() - n0
+
+    # end-to-end: pinned host -> device -> model -> host, every step, through the public API
+    # (speech_enhancement_b200.pipeline.HostPipeline: the copies of neighbouring steps overlap the kernels; every
+    # step's H2D and D2H are inside the timed region, the closing event is ordered behind the last D2H)
+    pipe = HostPipeline(model, dev)
+    out_len = pipe.output_length(host[0])
+    host_outs = [torch.empty((B, out_len), dtype=torch.float32).pin_memory() for _ in range(2)]
+
+    def step_e2e(i):
+        pipe.submit(host[i % 3], host_outs[i & 1])
+
+    step_e2e(0)
+    step_e2e(1)
+    pipe.synchronize()
+    ms_e2e = D.timed(step_e2e, steps, after=pipe.join)
+    pipe.synchronize()
+    clocks = sampler.stop() if (D.rank == 0 and full) else None
+
+    ms_graph = None
+    if with_graph:
+        from speech_enhancement_b200.graphs import GraphedInference
+        gi = GraphedInference(model)
+        for i in range(3):
+            gi(dev_in[i % 3])
+        ms_graph = D.timed(lambda i: gi(dev_in[i % 3]), steps)
+        del gi
+
+    audio_s = B * CLIP_S * D.world * steps
+    res = {'workload': config_dict(key, B, D.world)['workload'], 'metric': m['metric'],
+           'value': audio_s / (ms / 1e3), 'unit': UNIT, 'ms_per_step': ms / steps,
+           'e2e': {'value': audio_s / (ms_e2e / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': B * L * 4 * D.world,
+                   'd2h_bytes_per_step': B * out_len * 4 * D.world, 'ms_per_step': ms_e2e / steps},
+           'gpu_launches': int(launches), 'per_gpu_batch': B, 'n_gpus': D.world, 'gpu_model': gpu_what}
+    if ms_graph is not None:
+        res['cuda_graph_replay'] = {'ms_per_step': ms_graph / steps, 'value': audio_s / (ms_graph / 1e3), 'unit': UNIT}
+    if D.rank != 0:
+        del model, pipe
+        torch.cuda.empty_cache()
+        return None
+
+    # ---- per-stage profiling pass (rank 0 only, hooks + events; not part of `value`) ----
+    pk = peaks()
+    st = StageTimer()
+    nprof = min(steps, 5)
+    for i in range(nprof):
+        step(i)
+    tot = st.totals_ms()
+    st.close()
+    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm', 'linear', 'ccbam'):
+        tot.setdefault(k, 0.0)
+    win, hop, fft = m['stft']
+    T = (L + fft - win) // hop + 1
+    alg = {'stft': 4 * (L + (fft + 2) * T), 'istft': 4 * ((fft + 2) * T + out_len), 'mask': 4 * 6 * (fft // 2 + 1) * T}
+    stages = {}
+    for k in ('stft', 'istft', 'mask'):
+        t = tot[k] / nprof / 1e3
+        gbs = alg[k] * B / t / 1e9 if t else None
+        stages[k] = {'ms': t * 1e3, 'GB/s': gbs, 'frac_hbm': gbs / pk['hbm_gbs'] if gbs else None}
+    t_conv = tot['cconv'] / nprof / 1e3
+    tflops = m['conv_gflop'] * B / t_conv / 1e3
+    nconv = len(st.events.get('cconv', [])) // nprof
+    stages['cconv'] = {'ms': t_conv * 1e3, 'TFLOP/s': tflops, 'launches': nconv}
+    stages['cl2_convert_ms'] = tot['cl2'] / nprof
+    stages['lstm_recurrence_ms'] = tot['lstm'] / nprof
+    stages['lstm_linear_projections_ms'] = tot['linear'] / nprof
+    stages['ccbam_ms'] = tot['ccbam'] / nprof
+    stages['step_ms'] = ms / steps
+    stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / steps)
+    stages['stft_engine'] = model.stft._pick_engine('ConvSTFT', model.stft.weight[0, 0], False)
+    stages['istft_engine'] = model.istft._pick_engine('ConviSTFT', model.istft.window, True)
+    traffic, traffic_src = conv_traffic(key, B)
+    res['roofline'] = {'bound': 'tensor', 'kernel': f'complex conv stack ({nconv} conv launches per step)',
+                       'achieved': tflops, 'peak': pk['bf16_tflops_sustained'], 'unit': 'TFLOP/s',
+                       'frac': tflops / pk['bf16_tflops_sustained'],
+                       'frac_of_3pass_ceiling': tflops / (pk['bf16_tflops_sustained'] / 3),
+                       'traffic': traffic, 'traffic_unit': 'B per step (all conv launches)',
+                       'traffic_source': traffic_src,
+                       'algorithmic_bytes': m['act_mb'] * 1e6 * B,
+                       'peak_source': pk['source'] + ' bf16 dense (sustained)',
+                       'note': f'algorithmic FLOPs ({m["conv_gflop"]} GFLOP/utt); the tensor engine issues 3 bf16 '
+                               'passes per product, so the ceiling in algorithmic FLOPs is peak / 3'}
+    res['stages'] = stages
+    res['clocks'] = clocks
+
+    # ---- parity of the benchmarked batch ----
+    cpu_setup()
+    cpu_model, cpu_kind = build_cpu_model(key)
+    res['parity'] = parity_check(key, model, dev_in[0], pairs[0][0], pairs[0][1], cpu_model, cpu_kind)
+    del model, pipe, cpu_model
+    torch.cuda.empty_cache()
+    return res
+
+
+# ------------------------------------------------------------------------------------ training step (configs[3])
 def time_cpu_train(batch, iters):
-    """CARN step on the CPU oracle (B_cpu = 4), all host threads"""
+    """CARN step on the CPU arm (B_cpu = 4), all host threads"""
     from speech_enhancement_b200 import training
     from speech_enhancement_b200.synth import synth_noisy_speech
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1)
-    torch.set_num_threads(cores)
-    torch.set_flush_denormal(True)
-    model = build_oracle().train()
+    cpu_setup()
+    model, kind = build_cpu_model('carn_train')
+    model.train()
     opt, flat = training.make_optimizer(model), training.FlatGradients(model)
     mix, clean = synth_noisy_speech(batch, L, seed=1), synth_noisy_speech(batch, L, seed=2)
     training.train_step(model, opt, flat, mix, clean, reduce=False)
@@ -208,96 +506,99 @@ def time_cpu_train(batch, iters):
         ts.append(time.perf_counter() - t0)
     ts.sort()
     med = ts[len(ts) // 2]
-    return batch * CLIP_S / med, torch.get_num_threads(), med
+    return batch * CLIP_S / med, torch.get_num_threads(), med, kind
 
 
-def run_train(args):
-    """--model carn_train: one data-parallel training step per bench step."""
-    import torch.distributed as dist
+def train_parity(dev):
+    """loss and flat gradient of ONE CARN forward/backward on 2 x 4 s: CUDA build vs the CPU arm (same weights)"""
+    from speech_enhancement_b200 import training
+    from speech_enhancement_b200.synth import synth_noisy_speech
+    mix, clean = synth_noisy_speech(2, L, seed=31, return_clean=True)
+    res = {}
+    grads = {}
+    for where in ('cpu', 'gpu'):
+        if where == 'cpu':
+            model, kind = build_cpu_model('carn_train', seed=3)
+            res['vs'] = kind
+            a, b = mix, clean
+        else:
+            model, _ = build_gpu_model('carn_train', dev, seed=3)
+            a, b = mix.to(dev), clean.to(dev)
+        model.train()
+        flat = training.FlatGradients(model)
+        flat.zero()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            _, wav = model(a)
+            loss = training.si_snr_loss(training.pad_or_truncate(wav, b), b)
+            loss.backward()
+        grads[where] = (loss.item(), flat.buffer.detach().cpu().clone())
+        del model, flat
+    res['loss_cpu'], res['loss_gpu'] = grads['cpu'][0], grads['gpu'][0]
+    res['si_snr_delta_db'] = abs(grads['cpu'][0] - grads['gpu'][0])
+    res['grad_rel_l2'] = rel_l2(grads['gpu'][1], grads['cpu'][1])
+    res['ok'] = bool(res['si_snr_delta_db'] <= TOL_SISNR_DB and res['grad_rel_l2'] <= TOL_REL_L2)
+    res['tolerance'] = {'grad_rel_l2': TOL_REL_L2, 'si_snr_delta_db': TOL_SISNR_DB}
+    return res
+
+
+def bench_train(steps, warmup, D, full=True):
+    """--model carn_train: one data-parallel training step per bench step, GLOBAL batch 32 (strong scaling)."""
     from speech_enhancement_b200 import _abi, sharding, training
     from speech_enhancement_b200.synth import synth_noisy_speech
-
-    rank = int(os.environ.get('RANK', '0'))
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    local = int(os.environ.get('LOCAL_RANK', '0'))
-    GB = 32                                                     # global batch of configs[3]
-    if args.impl == 'reference':
-        if rank == 0:
-            value, cores, sec = time_cpu_train(4, max(args.steps, 1))
-            print(json.dumps({'impl': 'reference', 'metric': MODEL['metric'], 'value': value, 'unit': UNIT,
-                              'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3,
-                              'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32',
-                              'data': 'synthetic', 'config': {'workload': 'CARN fwd+bwd+AdamW step', 'global_batch': GB},
-                              'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                                               'sample': '4 x 4 s utterances per step on the CPU oracle'},
-                              'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-                              'gpu_launches': 0}), flush=True)
-        return
-    if not torch.cuda.is_available():
-        raise RuntimeError('bench.py: no CUDA device (speech_enhancement_b200 has no CPU path)')
-    torch.cuda.set_device(local)
-    dev = torch.device('cuda', local)
-    if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
+    m = MODELS['carn_train']
+    GB = 32
+    dev = D.dev
+    old_tf32 = torch.backends.cudnn.allow_tf32
     torch.backends.cudnn.allow_tf32 = False                     # fp32 math in the stock convolutions too
     lib = _abi.lib()
-    model = build_models(dev).train()
+    model, gpu_what = build_gpu_model('carn_train', dev)
+    model.train()
     opt, flat = training.make_optimizer(model), training.FlatGradients(model)
-    b0, b1 = sharding.shard_bounds(GB, rank, world)
+    b0, b1 = sharding.shard_bounds(GB, D.rank, D.world)
     host = [(synth_noisy_speech(GB, L, seed=200 + i)[b0:b1].pin_memory(),
              synth_noisy_speech(GB, L, seed=300 + i)[b0:b1].pin_memory()) for i in range(3)]
-    dev_in = [(m.to(dev), c.to(dev)) for m, c in host]
+    dev_in = [(a.to(dev), c.to(dev)) for a, c in host]
 
     def step(i):
         return training.train_step(model, opt, flat, *dev_in[i % 3])
 
     def step_e2e(i):
-        m, c = host[i % 3]
-        loss = training.train_step(model, opt, flat, m.to(dev, non_blocking=True), c.to(dev, non_blocking=True))
+        a, c = host[i % 3]
+        loss = training.train_step(model, opt, flat, a.to(dev, non_blocking=True), c.to(dev, non_blocking=True))
         return loss.item()                                      # D2H of the step's result
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(steps):
-            fn(i)
-        e1.record()
-        barrier()
-        return sharding.reduce_max(e0.elapsed_time(e1), device=dev)
-
-    for i in range(max(args.warmup, 3)):
+    for i in range(max(warmup, 3)):
         step(i)
-    sampler = ClockSampler(local)
-    if rank == 0:
+    sampler = ClockSampler(D.local)
+    if D.rank == 0 and full:
         sampler.start()
     n0 = lib.se_launch_count()
-    ms = timed(step, args.steps)
+    ms = D.timed(step, steps)
     launches = lib.se_launch_count() - n0
     step_e2e(0)
-    ms_e2e = timed(step_e2e, args.steps)
-    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e = D.timed(step_e2e, steps)
+    clocks = sampler.stop() if (D.rank == 0 and full) else None
+    # allreduce share: the same step without the gradient exchange (every rank runs it)
+    ms_noreduce = D.timed(lambda i: training.train_step(model, opt, flat, *dev_in[i % 3], reduce=False), steps)
     # per-stage profiling pass: EVERY rank steps (the step contains the allreduce), only rank 0 records
-    st = StageTimer() if rank == 0 else None
-    nprof = min(args.steps, 3)
+    st = StageTimer() if D.rank == 0 else None
+    nprof = min(steps, 3)
     for i in range(nprof):
         step(i)
-    barrier()
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+    D.barrier()
+    nb = b1 - b0
+    grad_bytes = flat.buffer.numel() * 4
+    del model, opt
+    torch.cuda.empty_cache()
+    if D.rank != 0:
+        torch.backends.cudnn.allow_tf32 = old_tf32
+        return None
     pk = peaks()
     tot = st.totals_ms()
     st.close()
-    win, hop, fft = MODEL['stft']
+    win, hop, fft = m['stft']
     T = (L + fft - win) // hop + 1
-    nb = b1 - b0
     alg = {'stft': 4 * (L + (fft + 2) * T), 'istft': 4 * ((fft + 2) * T + L), 'mask': 4 * 6 * (fft // 2 + 1) * T}
     alg.update(stft_bwd=alg['stft'], istft_bwd=alg['istft'], mask_bwd=4 * 10 * (fft // 2 + 1) * T)
     stages = {}
@@ -306,171 +607,122 @@ def run_train(args):
         stages[k] = {'ms': t * 1e3, 'GB/s': byt * nb / t / 1e9 if t else None,
                      'frac_hbm': byt * nb / t / 1e9 / pk['hbm_gbs'] if t else None}
     hot = sum(v['ms'] for v in stages.values())
-    stages['step_ms'] = ms / args.steps
-    stages['hot_path_share'] = hot / (ms / args.steps)
+    stages['step_ms'] = ms / steps
+    stages['step_without_allreduce_ms'] = ms_noreduce / steps
+    stages['hot_path_share'] = hot / (ms / steps)
     dom = max(alg, key=lambda k: stages[k]['ms'])
-    roofline = {'bound': 'hbm', 'kernel': f'{dom} (largest of this package\'s kernels in the step; the real convolutions '
-                                          'and the LSTM of CARN are stock cuDNN, out of scope)',
-                'achieved': stages[dom]['GB/s'], 'peak': pk['hbm_gbs'], 'unit': 'GB/s',
-                'frac': stages[dom]['frac_hbm'], 'traffic': None, 'peak_source': pk['source'] + ' HBM copy'}
-    audio_s = GB * CLIP_S * args.steps
-    cpu_val, cores, cpu_sec = time_cpu_train(4, 1)
-    grad_bytes = flat.buffer.numel() * 4
-    line = {'metric': MODEL['metric'], 'value': audio_s / (ms / 1e3), 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
-            'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'strong',
-            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': f'CARN (320/160/512, lstm 512) forward + SI-SNR + backward + clip 0.5 + AdamW, global '
-                                   f'batch {GB} x 4 s split {nb} per GPU, one flat-gradient allreduce '
-                                   f'({grad_bytes / 1e6:.1f} MB) per step', 'global_batch': GB, 'per_gpu_batch': nb,
-                       'parallelism': f'data-parallel x{world}, NCCL allreduce of the flat gradient',
-                       'l2_policy': 'inputs rotate over 3 buffers; activations exceed L2'},
-            'e2e': {'value': audio_s / (ms_e2e / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': 2 * nb * L * 4 * world,
-                    'd2h_bytes_per_step': 4 * world, 'ms_per_step': ms_e2e / args.steps},
-            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'stages': stages,
-            'cpu_baseline': {'value': cpu_val, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                             'sample': f'one CARN step at 4 x 4 s on the CPU oracle ({cpu_sec:.2f} s)'}}
-    print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    audio_s = GB * CLIP_S * steps
+    res = {'workload': f'CARN (320/160/512, lstm 512) forward + SI-SNR + backward + clip 0.5 + AdamW, global batch {GB} '
+                       f'x 4 s split {nb} per GPU, bucketed allreduce of the flat gradient ({grad_bytes / 1e6:.1f} MB) '
+                       'on a side stream overlapped with backward',
+           'metric': m['metric'], 'value': audio_s / (ms / 1e3), 'unit': UNIT, 'ms_per_step': ms / steps,
+           'scaling': 'strong', 'global_batch': GB, 'per_gpu_batch': nb, 'n_gpus': D.world, 'gpu_model': gpu_what,
+           'e2e': {'value': audio_s / (ms_e2e / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': 2 * nb * L * 4 * D.world,
+                   'd2h_bytes_per_step': 4 * D.world, 'ms_per_step': ms_e2e / steps},
+           'gpu_launches': int(launches), 'clocks': clocks,
+           'roofline': {'bound': 'hbm', 'kernel': f'{dom} (largest of this package\'s kernels in the step; the real '
+                                                  'convolutions and the LSTM of CARN are stock cuDNN, out of scope)',
+                        'achieved': stages[dom]['GB/s'], 'peak': pk['hbm_gbs'], 'unit': 'GB/s',
+                        'frac': stages[dom]['frac_hbm'], 'traffic': None, 'peak_source': pk['source'] + ' HBM copy'},
+           'stages': stages}
+    res['parity'] = train_parity(dev)
+    torch.backends.cudnn.allow_tf32 = old_tf32
+    return res
+
+
+def compact(r):
+    """other_configs entry: {workload, value, e2e, ms_per_step, roofline.frac, parity} (+ what identifies the run)"""
+    if r is None:
+        return None
+    out = {k: r[k] for k in ('workload', 'metric', 'value', 'unit', 'ms_per_step', 'per_gpu_batch', 'n_gpus') if k in r}
+    out['e2e'] = r['e2e']['value']
+    out['e2e_ms_per_step'] = r['e2e']['ms_per_step']
+    if 'cuda_graph_replay' in r:
+        out['cuda_graph_replay'] = r['cuda_graph_replay']
+    if 'scaling' in r:
+        out['scaling'] = r['scaling']
+    rf = r.get('roofline') or {}
+    out['roofline'] = {k: rf.get(k) for k in ('bound', 'frac', 'achieved', 'unit')}
+    st = r.get('stages') or {}
+    if 'cconv' in st:
+        out['stage_ms'] = {'cconv': st['cconv']['ms'], 'stft': st['stft']['ms'], 'istft': st['istft']['ms'],
+                           'mask': st['mask']['ms'], 'lstm': st['lstm_recurrence_ms'] + st['lstm_linear_projections_ms'],
+                           'ccbam': st['ccbam_ms']}
+        out['stft_frac_hbm'], out['istft_frac_hbm'] = st['stft']['frac_hbm'], st['istft']['frac_hbm']
+    if 'step_without_allreduce_ms' in st:
+        out['step_without_allreduce_ms'] = st['step_without_allreduce_ms']
+    out['parity'] = r.get('parity')
+    return out
 
 
 def run_ours(args):
-    import torch.distributed as dist
-    from speech_enhancement_b200 import _abi, sharding
-    from speech_enhancement_b200.synth import synth_noisy_speech
-
-    rank = int(os.environ.get('RANK', '0'))
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    local = int(os.environ.get('LOCAL_RANK', '0'))
-    if not torch.cuda.is_available():
-        raise RuntimeError('bench.py: no CUDA device (speech_enhancement_b200 has no CPU path)')
-    torch.cuda.set_device(local)
-    dev = torch.device('cuda', local)
-    if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
-    lib = _abi.lib()
-    if lib.se_device_ok() != 1:
+    from speech_enhancement_b200 import _abi
+    D = Dist()
+    if _abi.lib().se_device_ok() != 1:
         raise RuntimeError('bench.py: device is not compute capability 10.x')
+    key = args.model
+    m = MODELS[key]
+    if m.get('train'):
+        head = bench_train(args.steps, args.warmup, D)
+    else:
+        head = bench_inference(key, args.batch, args.steps, args.warmup, D)
+    others = []
+    if args.others and key == 'dccrn':
+        osteps = max(min(args.steps, 10), 2)
+        todo = [('dccrn', dict(B=1, with_graph=True)), ('dcunet20', dict(B=64)),
+                ('frcrn', dict(B=max(128 // D.world, 1))), ('carn_train', {})]
+        for k, kw in todo:
+            try:
+                if MODELS[k].get('train'):
+                    r = bench_train(osteps, 3, D, full=False)
+                else:
+                    r = bench_inference(k, kw['B'], osteps, 3, D, full=False, with_graph=kw.get('with_graph', False))
+            except Exception as e:                                   # an auxiliary config must not lose the headline
+                if D.world > 1:
+                    raise
+                r = {'workload': k, 'error': f'{type(e).__name__}: {e}'[:300]} if D.rank == 0 else None
+                if r is not None:
+                    others.append(r)
+                continue
+            if D.rank == 0:
+                others.append(compact(r))
+    if D.rank != 0:
+        D.close()
+        return 0
 
-    B = args.batch
-    model = build_models(dev)
-    host = [synth_noisy_speech(B, L, seed=100 + 7 * rank + i).pin_memory() for i in range(3)]
-    dev_in = [h.to(dev) for h in host]
-    out_len = model.istft(model.stft(dev_in[0][:1])).shape[1] if False else None
-
-    def step(i):
-        with torch.no_grad():
-            return model(dev_in[i % 3])[1]
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps, after=None):
-        """K steps bracketed by barrier + synchronize; device time via CUDA events; max over ranks."""
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(steps):
-            fn(i)
-        if after is not None:
-            after()
-        e1.record()
-        barrier()
-        return sharding.reduce_max(e0.elapsed_time(e1), device=dev)      # the slowest rank defines the step
-
-    for i in range(max(args.warmup, 3)):
-        step(i)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    n0 = lib.se_launch_count()
-    ms = timed(step, args.steps)
-    launches = lib.se_launch_count() - n0
-
-    # end-to-end: pinned host -> device -> model -> host, every step, through the public API
-    # (speech_enhancement_b200.pipeline.HostPipeline: the copies of neighbouring steps overlap the kernels; every
-    # step's H2D and D2H are inside the timed region, the closing event is ordered behind the last D2H)
-    from speech_enhancement_b200.pipeline import HostPipeline
-    pipe = HostPipeline(model, dev)
-    out_len = pipe.output_length(host[0])
-    host_outs = [torch.empty((B, out_len), dtype=torch.float32).pin_memory() for _ in range(2)]
-    host_out = host_outs[0]
-
-    def step_e2e(i):
-        pipe.submit(host[i % 3], host_outs[i & 1])
-
-    step_e2e(0)
-    step_e2e(1)
-    pipe.synchronize()
-    ms_e2e = timed(step_e2e, args.steps, after=pipe.join)
-    pipe.synchronize()
-    clocks = sampler.stop() if rank == 0 else None
-
-    audio_s = B * CLIP_S * world * args.steps
-    value, e2e_value = audio_s / (ms / 1e3), audio_s / (ms_e2e / 1e3)
-
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-
-    # ---- per-stage profiling pass (rank 0 only, hooks + events; not part of `value`) ----
-    pk = peaks()
-    st = StageTimer()
-    nprof = min(args.steps, 5)
-    for i in range(nprof):
-        step(i)
-    tot = st.totals_ms()
-    st.close()
-    for k in ('stft', 'istft', 'mask', 'cconv', 'cl2', 'lstm', 'linear', 'ccbam'):
-        tot.setdefault(k, 0.0)
-    win, hop, fft = MODEL['stft']
-    T = (L + fft - win) // hop + 1
-    Lp = out_len or (T - 1) * hop + win - fft
-    alg = {'stft': 4 * (L + (fft + 2) * T), 'istft': 4 * ((fft + 2) * T + Lp), 'mask': 4 * 6 * (fft // 2 + 1) * T}
-    stages = {}
-    for k in ('stft', 'istft', 'mask'):
-        t = tot[k] / nprof / 1e3
-        gbs = alg[k] * B / t / 1e9
-        stages[k] = {'ms': t * 1e3, 'GB/s': gbs, 'frac_hbm': gbs / pk['hbm_gbs']}
-    t_conv = tot['cconv'] / nprof / 1e3
-    tflops = MODEL['conv_gflop'] * B / t_conv / 1e3
-    stages['cconv'] = {'ms': t_conv * 1e3, 'TFLOP/s': tflops, 'launches': len(st.events.get('cconv', [])) // nprof}
-    stages['cl2_convert_ms'] = tot['cl2'] / nprof
-    stages['lstm_recurrence_ms'] = tot['lstm'] / nprof
-    stages['lstm_linear_projections_ms'] = tot['linear'] / nprof
-    stages['ccbam_ms'] = tot['ccbam'] / nprof
-    stages['step_ms'] = ms / args.steps
-    stages['hot_path_share'] = (tot['stft'] + tot['istft'] + tot['mask'] + tot['cconv']) / nprof / (ms / args.steps)
-    roofline = {'bound': 'tensor', 'kernel': f'complex conv stack ({len(st.events.get("cconv", [])) // nprof} conv launches per step)',
-                'achieved': tflops, 'peak': pk['bf16_tflops_sustained'], 'unit': 'TFLOP/s',
-                'frac': tflops / pk['bf16_tflops_sustained'],
-                # dram__bytes_read + write summed over the 11 conv GEMM launches of one step from the ncu --set full
-                # captures (profiles/r1c_gemm_full_summary.txt, B=64: 25.46 GB; the eight launches re-captured in
-                # profiles/r1e_gemm_full_summary.txt / r1g_gemm_full_summary.txt agree within 2 %), scaled per utterance
-                'traffic': 25.458e9 / 64 * B if args.model == 'dccrn' else None,
-                'traffic_unit': 'B per step (all conv GEMM launches)',
-                'peak_source': pk['source'] + ' bf16 dense (sustained)',
-                'note': f'algorithmic FLOPs ({MODEL["conv_gflop"]} GFLOP/utt); the tensor engine issues 3 bf16 passes per product'}
-
-    cpu_val, cores, cpu_sec = time_cpu_oracle(2, iters=5, warmup=1)
-    stages['stft_engine'] = model.stft._pick_engine('ConvSTFT', model.stft.weight[0, 0], False)
-    stages['istft_engine'] = model.istft._pick_engine('ConviSTFT', model.istft.window, True)
-    line = {'metric': MODEL['metric'], 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
-            'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32 (bf16x3 split operands, fp32 accumulate)',
-            'data': 'synthetic', 'config': config_dict(B, world),
-            'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': B * L * 4 * world,
-                    'd2h_bytes_per_step': int(host_out.numel()) * 4 * world, 'ms_per_step': ms_e2e / args.steps},
-            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'stages': stages,
-            'cpu_baseline': {'value': cpu_val, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                             'sample': f'2 x 4 s utterances, median of 5 ({cpu_sec:.2f} s each); CPU oracle = '
-                                       'torch-CPU restatement of the reference path on the host cores, flush-denormal on'}}
+    if m.get('train'):
+        cpu_val, cores, cpu_sec, kind = time_cpu_train(4, 1)
+        cpu = {'value': cpu_val, 'unit': UNIT, 'cores': cores, 'kind': kind,
+               'sample': f'one CARN step at 4 x 4 s ({cpu_sec:.2f} s); ' + cpu_kind_text(kind)}
+        cfg = {'workload': head['workload'], 'global_batch': head['global_batch'], 'per_gpu_batch': head['per_gpu_batch'],
+               'parallelism': f'data-parallel x{D.world}, NCCL allreduce of the flat gradient',
+               'l2_policy': 'inputs rotate over 3 buffers; activations exceed L2', 'gpu_model': head['gpu_model']}
+        scaling, dtype = 'strong', 'f32'
+    else:
+        v1, cores, s1, kind = time_cpu_forward(key, 1, iters=5, warmup=1)
+        v8, _, s8, _ = time_cpu_forward(key, 8, iters=3, warmup=1)
+        best, nb = (v8, 8) if v8 >= v1 else (v1, 1)
+        cpu = {'value': best, 'unit': UNIT, 'cores': cores, 'kind': kind,
+               'batch1': {'value': v1, 'latency_ms': s1 * 1e3}, 'batch8': {'value': v8, 'ms': s8 * 1e3},
+               'sample': f'{nb} x 4 s utterances (the better of batch 1, median of 5, and batch 8, median of 3); '
+                         + cpu_kind_text(kind)}
+        cfg = config_dict(key, args.batch, D.world, head['gpu_model'])
+        scaling, dtype = 'weak', 'f32 (bf16x3 split operands, fp32 accumulate)'
+    line = {'metric': m['metric'], 'value': head['value'], 'unit': UNIT, 'n_gpus': D.world, 'steps': args.steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': head['ms_per_step'], 'higher_is_better': True,
+            'scaling': scaling, 'vs_baseline': None, 'dtype': dtype, 'data': 'synthetic', 'config': cfg,
+            'e2e': head['e2e'], 'gpu_launches': head['gpu_launches'], 'clocks': head['clocks'],
+            'roofline': head['roofline'], 'stages': head['stages'], 'parity': head['parity'], 'cpu_baseline': cpu}
+    if others:
+        line['other_configs'] = others
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    D.close()
+    bad = [] if head['parity']['ok'] else ['headline']
+    bad += [o['workload'][:40] for o in others if o and o.get('parity') and not o['parity']['ok']]
+    if bad:
+        print(f'bench.py: parity bar missed: {bad}', file=sys.stderr)
+        return 3
+    return 0
 
 
 def main():
@@ -482,16 +734,14 @@ def main():
                     help='4 s utterances per GPU per step')
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--model', default=os.environ.get('SE_BENCH_MODEL', 'dccrn'), choices=sorted(MODELS))
+    ap.add_argument('--no-others', dest='others', action='store_false',
+                    help='headline only: skip the other BASELINE configurations')
     args = ap.parse_args()
-    global MODEL
-    MODEL = MODELS[args.model]
-    if MODEL.get('train'):
-        return run_train(args)
     if args.impl == 'reference':
         run_reference(args)
-    else:
-        run_ours(args)
+        return 0
+    return run_ours(args)
 
 
 if __name__ == '__main__':
-    main()
+    sys.exit(main())

@@ -9,7 +9,8 @@ from .conv_stft import ConvSTFT, ConviSTFT, init_kernels
 from .modules import (ComplexConv2d, ComplexConvTranspose2d, ComplexBatchNorm2d, ComplexLSTM, ComplexLinear,
                       ComplexPReLU, ComplexReLU, ComplexLeakyReLU, complex_concat, split_complex, merge_real_imag)
 from . import functional
+from ._abi import invalidate_caches
 
 __all__ = ['ConvSTFT', 'ConviSTFT', 'init_kernels', 'ComplexConv2d', 'ComplexConvTranspose2d',
            'ComplexBatchNorm2d', 'ComplexLSTM', 'ComplexLinear', 'ComplexPReLU', 'ComplexReLU',
-           'ComplexLeakyReLU', 'complex_concat', 'split_complex', 'merge_real_imag', 'functional']
+           'ComplexLeakyReLU', 'complex_concat', 'split_complex', 'merge_real_imag', 'functional', 'invalidate_caches']

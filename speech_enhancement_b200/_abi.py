@@ -119,6 +119,51 @@ def check(rc):
         raise _EXC.get(rc, RuntimeError)(f'libse_b200: {msg} (code {rc})')
 
 
+# ---- derived-operand caches (packed conv weights, folded BN operands, linear operands, STFT bases) ------------
+# Every cache is keyed on the (data_ptr, _version, device) of the tensors it was derived from.  Autograd's version
+# counter sees optimizer steps, load_state_dict and in-place ops on the parameter itself, but NOT writes through
+# `param.data` (reference utils.py:50-69 initialize_params, complex_nn.py:205-209, EMA swaps): `.data` is a detached
+# alias with its own counter.  After such an edit call `invalidate_caches()` (or `module.invalidate()`); nn.Module
+# `_apply` (.to / .cuda / .float) and `_load_from_state_dict` of this package's modules do it themselves.
+# SE_VERIFY_CACHES=1 adds a checksum of every source tensor to the key (one device sync per lookup: debugging only).
+_cache_epoch = 0
+_VERIFY = os.environ.get('SE_VERIFY_CACHES', '0') not in ('', '0')
+
+
+def invalidate_caches():
+    """drop every derived operand of this package (they are rebuilt on next use)"""
+    global _cache_epoch
+    _cache_epoch += 1
+
+
+def cache_key(tensors, *extra):
+    key = [_cache_epoch]
+    for t in tensors:
+        if t is None:
+            key.append(None)
+            continue
+        key.append((t.data_ptr(), t._version, t.device))
+        if _VERIFY:
+            d = t.detach().double()
+            key.append((float(d.sum()), float(d.abs().sum())))
+    return tuple(key) + tuple(extra)
+
+
+class InvalidatesCaches:
+    """nn.Module mixin: moving / casting the module or loading a state_dict drops the derived operands"""
+
+    def invalidate(self):
+        invalidate_caches()
+
+    def _apply(self, fn, *args, **kwargs):
+        invalidate_caches()
+        return super()._apply(fn, *args, **kwargs)
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        invalidate_caches()
+        return super()._load_from_state_dict(*args, **kwargs)
+
+
 # ---- optional per-stage timing (bench.py installs a timer; no-op otherwise) ----------------------
 _timer = None
 

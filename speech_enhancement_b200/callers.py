@@ -391,7 +391,8 @@ class CCBAM(nn.Module):
             blk = self.__dict__['_sa_block'] = FusedBlock(conv.conv, conv.norm, conv.act)
         ops = blk._operands()
         lins = [fc[0].linear.real_linear, fc[0].linear.imag_linear, fc[1].linear.real_linear, fc[1].linear.imag_linear]
-        key = tuple((l.weight.data_ptr(), l.weight._version) for l in lins) + (id(ops['packed']),)
+        from . import _abi
+        key = _abi.cache_key([l.weight for l in lins], id(ops['packed']))
         c = self.__dict__.get('_attn_ops')
         if c is None or c[0] != key:
             with torch.no_grad():

@@ -170,7 +170,7 @@ class FusedBlock:
             if norm.affine:
                 ts += [norm.Wrr, norm.Wri, norm.Wii, norm.Br, norm.Bi]
         ts += list(slope_t)
-        key = tuple((t.data_ptr(), t._version) for t in ts)
+        key = _abi.cache_key(ts)
         if key == self._key:
             return self._ops
         with torch.no_grad():
@@ -366,7 +366,7 @@ class LinearOperand:
         for w, b in parts:
             flat.append(w)
             flat.extend(b if isinstance(b, (tuple, list)) else [b])
-        key = tuple((t.data_ptr(), t._version, t.device) if t is not None else None for t in flat)
+        key = _abi.cache_key(flat)
         if key != self._key:
             with torch.no_grad():
                 ws, bs = [], []

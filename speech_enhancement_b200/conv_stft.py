@@ -85,12 +85,6 @@ def _is_dft_basis(weight, window, fft, inverse):
     return bool(((w - ref).abs().max() <= 2e-6 * ref.abs().max()).item())
 
 
-def _no_grad_only(name, *tensors):
-    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
-        raise RuntimeError(f'{name}: backward is not implemented in this build; '
-                           'call under torch.no_grad() / with inputs that do not require grad')
-
-
 def _frames_operand(w, hop):
     """basis [C2, 1, win] regrouped for the framing projection (a 1 x J convolution over hop-sample pixels,
     `hop` input channels): [C2][hop][J], output rows in chunks of <= 256."""
@@ -183,7 +177,7 @@ class _IstftFn(torch.autograd.Function):
         return None, ctx.mod._synthesize_adjoint(g.contiguous().float(), ctx.T, ctx.start), None, None
 
 
-class ConvSTFT(nn.Module):
+class ConvSTFT(_abi.InvalidatesCaches, nn.Module):
     def __init__(self, window_size, hop_size, fft_size=None, win_type='hann', center=True,
                  return_mag_phase=False, fix=True):
         super().__init__()
@@ -204,7 +198,7 @@ class ConvSTFT(nn.Module):
         """the FFT kernels apply: framing covered and `weight` is the closed-form basis (checked once per
         weight version, on the device)"""
         w = self.weight
-        key = (w.data_ptr(), w._version, window.data_ptr(), window._version, w.device)
+        key = _abi.cache_key((w, window))
         c = self.__dict__.get('_fft_check')
         if c is None or c[0] != key:
             ok = (_abi.lib().se_stft_fft_supported(self.window_size, self.hop_size, self.fft_size) == 1
@@ -227,7 +221,7 @@ class ConvSTFT(nn.Module):
 
     def _cached(self, slot, build):
         w = self.weight
-        key = (slot, w.data_ptr(), w._version, w.device)
+        key = _abi.cache_key((w,), slot)
         c = self.__dict__.setdefault('_tc_cache', {})
         if c.get(slot, (None,))[0] != key:
             with torch.no_grad():
@@ -317,7 +311,7 @@ class ConvSTFT(nn.Module):
         return mags, phase
 
 
-class ConviSTFT(nn.Module):
+class ConviSTFT(_abi.InvalidatesCaches, nn.Module):
     def __init__(self, window_size, hop_size, fft_size=None, win_type='hann', center=True, fix=True):
         super().__init__()
         self.fft_size = window_size if fft_size is None else fft_size
@@ -343,7 +337,7 @@ class ConviSTFT(nn.Module):
     def _ola_scale(self, T, J):
         """1 / (sum of squared windows + 1e-8) per output sample (conv_stft.py:101-106), [Q*hop]."""
         window = self.window
-        key = (T, window.data_ptr(), window._version, window.device)
+        key = _abi.cache_key((window,), T)
         sc = self._scale.get(key)
         if sc is None:
             hop, win = self.hop_size, self.window_size
@@ -398,7 +392,7 @@ class ConviSTFT(nn.Module):
     def _packed_basis(self):
         """inverse basis regrouped per hop phase (se_istft_pack_basis); rebuilt when `weight` changes."""
         w = self.weight
-        key = (w.data_ptr(), w._version, w.device)
+        key = _abi.cache_key((w,))
         if self._packed_key != key:
             c2, _, win = w.shape
             J = -(-win // self.hop_size)

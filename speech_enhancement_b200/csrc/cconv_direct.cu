@@ -273,7 +273,8 @@ extern "C" int se_cconv_small_cin(const float* x, int64_t xs_b, int64_t xs_c, in
     if (kh == 3 && kw == 3 && sh == 1 && sw == 1) return se::launch_first<3, 3, 1, 1>(p, B, (cudaStream_t)stream);
   }
   const int smem = K * Cr * 4;
-  static int smem_attr = 48 * 1024;
+  static se::PerDevice<int> smem_attr_pd(48 * 1024);
+  int& smem_attr = smem_attr_pd.get();
   if (smem > smem_attr) {                         // only the 32-wide pass can exceed the default
     SE_CUDA(cudaFuncSetAttribute(se::cconv_small_cin_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     smem_attr = smem;
@@ -364,7 +365,8 @@ int cconv_fwd_small_cout(bool transposed, const float* x, const float* packed, c
   if (g.Ho > 65535 || B > 65535) return fail(SE_ERR_UNSUPPORTED, "small-Cout direct kernel: tensor too large");
   SmallCoutParams p{x, packed, bias, y, transposed ? 1 : 0, g.Cin2, g.H, g.W, g.Cout2, g.kh, g.kw, g.sh, g.sw,
                     g.ph, g.pw, g.Ho, g.Wo, 1.f};
-  static int smem_attr = 48 * 1024;
+  static se::PerDevice<int> smem_attr_pd(48 * 1024);
+  int& smem_attr = smem_attr_pd.get();
   if (smem > smem_attr) {
     SE_CUDA(cudaFuncSetAttribute(cconv_small_cout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     smem_attr = smem;

@@ -855,7 +855,8 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     if (rc != SE_OK) return rc;
   }
   const int smem = p.SA * p.a_slot + p.SB * p.b_unit + 1024;
-  static int smem_attr = 0;
+  static se::PerDevice<int> smem_attr_pd(0);
+  int& smem_attr = smem_attr_pd.get();
   if (smem > smem_attr) {
     SE_CUDA(cudaFuncSetAttribute(cconv_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     SE_CUDA(cudaFuncSetAttribute(cconv_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

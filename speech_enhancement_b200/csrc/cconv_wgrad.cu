@@ -321,7 +321,8 @@ extern "C" int se_cconv_wgrad(const void* u_nc2, int Cu, int Hu, int Wu, const v
   rc = se::make_nc2_map(&tmV, v_gather, B, Cv, Hv, Wu, Wup, p.n_tile, kw);
   if (rc != SE_OK) return rc;
   const int smem = p.stages * p.stage_bytes + 1024;
-  static int smem_attr = 0;
+  static se::PerDevice<int> smem_attr_pd(0);
+  int& smem_attr = smem_attr_pd.get();
   if (smem > smem_attr) {
     SE_CUDA(cudaFuncSetAttribute(se::cconv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     smem_attr = smem;

@@ -38,8 +38,25 @@ inline int check_launch(const char* what) {
   do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
          return se::fail(SE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
 
+// Per-device host-side state.  cudaFuncSetAttribute (the > 48 KB dynamic shared memory opt-in) and the SM count
+// belong to a DEVICE, not to the process: a flag set while cuda:0 was current says nothing about cuda:1
+// (model.to('cuda:1'), nn.DataParallel, tests that touch two GPUs in one process).  `get()` is the slot of the
+// device that is current on the calling thread.  Concurrent first calls may both run the (idempotent) set-up.
+constexpr int kMaxDevices = 64;
+inline int current_device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) dev = 0;
+  return dev;
+}
+template <typename T> struct PerDevice {
+  T v[kMaxDevices];
+  explicit PerDevice(T init) { for (int i = 0; i < kMaxDevices; ++i) v[i] = init; }
+  T& get() { return v[current_device_slot()]; }
+};
+
 inline int num_sms() {
-  static int n = 0;
+  static PerDevice<int> count(0);
+  int& n = count.get();
   if (n == 0) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess ||

@@ -394,7 +394,8 @@ template <int H, int KR, int R>
 static int launch_lstm2(const float* pre, int64_t pre_ld, const float* w_hh0, const float* w_hh1, float* h_out0,
                         float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
   const int smem = ((H - KR) * 4 * H + 2 * R * H) * (int)sizeof(float);
-  static bool attr_set = false;
+  static se::PerDevice<bool> attr_set_pd(false);
+  bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
     SE_CUDA(cudaFuncSetAttribute(lstm_rec2_kernel<H, KR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
@@ -411,7 +412,8 @@ static int launch_lstm(const float* pre, int64_t pre_ld, const float* w_hh0, con
                        float* h_out1, int nl, int64_t N, int64_t T, cudaStream_t s) {
   constexpr int G = 4 * H;
   const int smem = ((H - KR) * G + R * H + R * G) * (int)sizeof(float);
-  static bool attr_set = false;
+  static se::PerDevice<bool> attr_set_pd(false);
+  bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
     SE_CUDA(cudaFuncSetAttribute(lstm_rec_kernel<H, KR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;

@@ -502,7 +502,8 @@ extern "C" int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float
   int xs_cap = ((TILE - 1) * hop + NFFT + 3) & ~3;
   size_t smem = (size_t)(TILE / 2) * ZPITCH * sizeof(float2) + 16 * 32 * sizeof(float2) + NFFT * sizeof(float) +
                 2 * (size_t)xs_cap * sizeof(float);
-  static bool attr_set = false;
+  static se::PerDevice<bool> attr_set_pd(false);
+  bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
     SE_CUDA(cudaFuncSetAttribute(stft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024));
     attr_set = true;
@@ -531,7 +532,8 @@ extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const f
   int64_t tiles = (Q + tq - 1) / tq;
   SE_REQUIRE(tiles * B < (1ll << 31), "se_istft_fft_fwd: batch x frame count too large");
   size_t smem = (size_t)(fft + 2) * IPITCH * sizeof(float) + (size_t)WARPS * 16 * TPITCH * sizeof(float2);
-  static bool attr_set = false;
+  static se::PerDevice<bool> attr_set_pd(false);
+  bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
     SE_CUDA(cudaFuncSetAttribute(istft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set = true;

@@ -98,7 +98,7 @@ def lstm_pair_forward(owner, lstms, x, engine):
     return outs
 
 
-class ComplexLinear(nn.Module):
+class ComplexLinear(_abi.InvalidatesCaches, nn.Module):
     """independent real / imaginary linears on the last-dim halves (complex_nn.py:93-113)."""
 
     def __init__(self, in_channels, out_channels, **kwargs):
@@ -129,7 +129,7 @@ class ComplexLinear(nn.Module):
         return merge_real_imag(x, self.real_linear(real), self.imag_linear(imag), dim=-1)
 
 
-class ComplexLSTM(nn.Module):
+class ComplexLSTM(_abi.InvalidatesCaches, nn.Module):
     """complex LSTM as four real LSTM passes (complex_nn.py:115-145)."""
 
     def __init__(self, in_channels, hidden_channels, **kwargs):
@@ -179,7 +179,7 @@ class ComplexLSTM(nn.Module):
         self.imag_lstm.flatten_parameters()
 
 
-class ComplexBatchNorm2d(nn.Module):
+class ComplexBatchNorm2d(_abi.InvalidatesCaches, nn.Module):
     """2x2 whitening batch norm of Trabelsi et al. (complex_nn.py:148-329)."""
 
     def __init__(self, num_features, eps=1e-5, momentum=0.1, affine=True, track_running_stats=True,

@@ -47,7 +47,7 @@ def _pair(v):
 
 
 # --------------------------------------------------------------------------- the two hot layers
-class ComplexConv(nn.Module):
+class ComplexConv(_abi.InvalidatesCaches, nn.Module):
     """Shared forward of the two complex conv layers (complex_nn.py:45-65)."""
     _transposed = False
     engine = _abi.ENGINE_AUTO          # class-level knob: ENGINE_AUTO / ENGINE_SIMT / ENGINE_UMMA
@@ -59,11 +59,13 @@ class ComplexConv(nn.Module):
         self._pack = None
         self._pack_key = None
 
-    # packed operand cache: rebuilt after optimizer.step() / load_state_dict / re-init
+    # packed operand cache, keyed on (data_ptr, _version) of the weights: rebuilt after optimizer.step(),
+    # load_state_dict, .to() and in-place ops on the parameters.  Writes through `weight.data` (reference
+    # utils.py:50-69 initialize_params) are invisible to the version counter: call `invalidate()` after them.
     def _packed(self):
         rc, ic = self.real_conv, self.imag_conv
         ts = [rc.weight, ic.weight] + ([rc.bias, ic.bias] if rc.bias is not None else [])
-        key = tuple((t.data_ptr(), t._version) for t in ts) + (rc.weight.device,)
+        key = _abi.cache_key(ts)
         if self._pack_key != key:
             wr = _abi.require_cuda_f32(rc.weight.detach(), 'real_conv.weight').contiguous()
             wi = _abi.require_cuda_f32(ic.weight.detach(), 'imag_conv.weight').contiguous()
@@ -91,6 +93,15 @@ class ComplexConv(nn.Module):
                                'by the B200 kernels')
         if getattr(rc, 'padding_mode', 'zeros') != 'zeros' or isinstance(rc.padding, str):
             raise RuntimeError(f'{type(self).__name__}: only numeric zero padding is supported')
+        # real_conv / imag_conv are parameter HOLDERS whose forward never runs, so anything that recomputes
+        # `.weight` in a forward pre-hook (torch.nn.utils.weight_norm, reference utils.py:54-55 weight_norm=True) or
+        # through a parametrization would silently be ignored
+        for holder in (rc, self.imag_conv):
+            if holder._forward_pre_hooks or getattr(holder, 'parametrizations', None) is not None \
+                    or not isinstance(holder._parameters.get('weight'), nn.Parameter):
+                raise RuntimeError(f'{type(self).__name__}: weight_norm / parametrizations / forward pre-hooks on '
+                                   'real_conv / imag_conv are not supported (their forward is never called); '
+                                   'remove them (torch.nn.utils.remove_weight_norm) before the first forward')
 
     def forward(self, x):
         real, imag = split_complex(x)

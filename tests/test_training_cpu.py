@@ -35,7 +35,9 @@ def _worker(rank, world, port, out):
     dist.init_process_group('gloo', rank=rank, world_size=world)
     try:
         model = _model()
-        opt, flat = training.make_optimizer(model), training.FlatGradients(model)
+        # 1 MB buckets: several asynchronous exchanges start from the gradient hooks while backward still runs
+        opt, flat = training.make_optimizer(model), training.FlatGradients(model, bucket_bytes=1 << 20)
+        assert len(flat.buckets) > 4 and sum(b.numel() for b in flat.buckets) == flat.buffer.numel()
         mix, clean = _data()
         loss = training.train_step(model, opt, flat, sharding.shard_batch(mix), sharding.shard_batch(clean))
         torch.save({'grad': flat.buffer.clone(), 'loss': loss, 'w': model.linear.weight.detach().clone()},
@@ -73,7 +75,7 @@ def test_flat_gradients_are_views_and_survive_zero_grad():
     assert sum(p.numel() for p in model.parameters()) == flat.buffer.numel()
     opt.zero_grad(set_to_none=True)
     flat.rebind()
-    p = next(model.parameters())
+    p = list(model.parameters())[-1]              # reverse registration order: the last parameter leads the buffer
     assert p.grad.data_ptr() == flat.buffer.data_ptr()
     x = torch.randn(1, 4000) * 0.1
     est = model(x)[1]
