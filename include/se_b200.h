@@ -95,6 +95,22 @@ SE_API int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float* wi
 SE_API int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
                             const float* scale, int64_t crop_front, int64_t out_len, float* out, void* stream);
 
+/* ---- PCM_S 16 wire format fused into the FFT engine -----------------------------------
+ * The reference reads 16-bit PCM wav files (audio_dataset.py:12-21; torchaudio.load scales by 1 / 32768) and writes
+ * them (mix_audio.py:144-146, trainer.py:255-262: torchaudio.save(encoding="PCM_S", bits_per_sample=16), i.e.
+ * FFmpeg's av_clip_int16(lrintf(x * 2^15))).
+ *   se_stft_fft_fwd_pcm16   se_stft_fft_fwd on int16 samples: the conversion happens in the stage load
+ *   se_istft_fft_fwd_pcm16  se_istft_fft_fwd writing int16: clamp(-1, 1) (_2008_00264_dccrn.py:184) + round to
+ *                           nearest + saturate in the overlap-add epilogue
+ *   se_pcm16_to_f32 / se_pcm16_from_f32   the same two conversions as standalone passes over n samples (for the
+ *                           framings the FFT engine does not cover)                                               */
+SE_API int se_stft_fft_fwd_pcm16(const int16_t* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
+                                 int pad, float* out, int64_t T, void* stream);
+SE_API int se_istft_fft_fwd_pcm16(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
+                                  const float* scale, int64_t crop_front, int64_t out_len, int16_t* out, void* stream);
+SE_API int se_pcm16_to_f32(const int16_t* x, int64_t n, float* y, void* stream);
+SE_API int se_pcm16_from_f32(const float* x, int64_t n, int16_t* y, void* stream);
+
 /* ---- ComplexConv2d / ComplexConvTranspose2d (complex_nn.py:52-91) ----------------------------
  * se_cconv_pack_weight: Wr, Wi are the real_conv / imag_conv weights
  *   (conv: [Co, Ci, kh, kw]; transposed: [Ci, Co, kh, kw]); packed is the real GEMM operand
@@ -174,6 +190,13 @@ typedef struct se_cconv_args {
   /* optional real channel count of every source (0 = src_Cp): channels [src_C, src_Cp) are zero in the CL2
    * activations and in the prepared weights, so the engine skips 16-channel k-steps that are all padding. */
   int src_C[2];
+  /* optional phase folding (0 or 1 = off): the launch is a stride-1 forward convolution whose Cout2 = fold_h * fold_w *
+   * fold_cg accumulator columns are the output phases of a ComplexConvTranspose2d with stride (fold_h, fold_w) side by
+   * side -- column group ph = r * fold_w + s of quotient pixel (q, p) is output pixel (q * fold_h + r, p * fold_w + s),
+   * channel = column - ph * fold_cg (< fold_cout2).  Ho, Wo are the real output extent; `wq` / `bias` are built for the
+   * folded columns (zero weight blocks where a phase has no tap at an input offset).  One wide MMA per input offset
+   * replaces one narrow MMA per kernel tap: complex_nn.py:80-91 layers with few output channels.                    */
+  int fold_h, fold_w, fold_cg, fold_cout2;
 } se_cconv_args;
 SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);
 /* fp32 x[b*xs_b + c*xs_c + h*xs_h + w] -> CL2 (same as se_cl2_from_nchw for arbitrary outer strides). */
@@ -254,6 +277,21 @@ SE_API int se_ccbam_channel_attn(const float* partial, int nblk, int64_t P, cons
                                  int C, int Cp, int R2, float* ca, void* stream);
 SE_API int se_ccbam_spatial_attn(const float* pooled, const float* packed, const float* bias, int64_t B, int H, int W,
                                  float* sa, void* stream);
+
+/* ---- train-mode ComplexBatchNorm2d (complex_nn.py:244-322; SURVEY.md 8f rank 1, the half that is not folded) ------
+ * x, y, g, dx [B, 2C, H, W] NCHW fp32, channels [0, C) real and [C, 2C) imaginary.
+ *   se_cbn_splits     S = number of partial-sum slots per channel for this shape
+ *   se_cbn_stats      partial [C][S][5] (fp64): sum xr, xi, xr^2, xi^2, xr*xi -- the batch statistics of :266-281
+ *   se_cbn_apply      y = Z x + c with coef [6][C] = Zrr, Zri, Zir, Zii, cr, ci (Z = W V^-1/2, c = B - Z M; :283-322)
+ *   se_cbn_bwd_stats  partial [C][S][6] (fp64): sum gr, gi, gr*xr, gr*xi, gi*xr, gi*xi
+ *   se_cbn_bwd_apply  dx = Z^T g + a0 + A x with coef [10][C] = Zrr, Zri, Zir, Zii, ar0, arr, ari, ai0, air, aii
+ * The C-sized algebra between the passes (means, covariance, whitening, its derivative) stays on the host side.     */
+SE_API int se_cbn_splits(int64_t B, int C, int H, int W);
+SE_API int se_cbn_stats(const float* x, int64_t B, int C, int H, int W, double* partial, void* stream);
+SE_API int se_cbn_apply(const float* x, const float* coef, int64_t B, int C, int H, int W, float* y, void* stream);
+SE_API int se_cbn_bwd_stats(const float* x, const float* g, int64_t B, int C, int H, int W, double* partial, void* stream);
+SE_API int se_cbn_bwd_apply(const float* x, const float* g, const float* coef, int64_t B, int C, int H, int W, float* dx,
+                            void* stream);
 
 /* ---- mask / magnitude-phase math (file:line per SE_MASK_* above) -----------------------------
  * Four input planes, each [B, F, T] addressed as base + b*bstride + f*fstride + t (elements),

@@ -26,10 +26,10 @@ def main():
     import bench
     from speech_enhancement_b200 import chain
     from speech_enhancement_b200.synth import synth_noisy_speech
-    bench.MODEL = bench.MODELS[a.model]
     pk = bench.peaks()
     dev = torch.device('cuda:0')
-    model = bench.build_models(dev)
+    model, what = bench.build_gpu_model(a.model, dev)
+    print(f'# model: {what}')
     x = synth_noisy_speech(a.batch, bench.L, seed=1).to(dev)
     rec = []
     orig_call, orig_first = chain.FusedBlock.__call__, chain.FusedBlock.first_layer

@@ -23,8 +23,11 @@ COLS = [
 
 
 def main(path):
-    raw = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
-    rows = list(csv.reader(io.StringIO(raw)))
+    if path.endswith('.csv'):
+        raw = open(path).read()
+    else:
+        raw = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = [r for r in csv.reader(io.StringIO(raw)) if len(r) > 5]
     hdr, units, data = rows[0], rows[1], rows[2:]
     idx = {n: hdr.index(n) for n, _ in COLS if n in hdr}
     kn = hdr.index('Kernel Name')

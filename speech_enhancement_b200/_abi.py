@@ -60,12 +60,21 @@ _SIGS = {
     'se_ccbam_apply': (C.c_int, [_P, _P, _P, _L, _L, _I, _I, _P, _P]),
     'se_ccbam_channel_attn': (C.c_int, [_P, _I, _L, _P, _P, _L, _I, _I, _I, _P, _P]),
     'se_ccbam_spatial_attn': (C.c_int, [_P, _P, _P, _L, _I, _I, _P, _P]),
+    'se_cbn_splits': (C.c_int, [_L, _I, _I, _I]),
+    'se_cbn_stats': (C.c_int, [_P, _L, _I, _I, _I, _P, _P]),
+    'se_cbn_apply': (C.c_int, [_P, _P, _L, _I, _I, _I, _P, _P]),
+    'se_cbn_bwd_stats': (C.c_int, [_P, _P, _L, _I, _I, _I, _P, _P]),
+    'se_cbn_bwd_apply': (C.c_int, [_P, _P, _P, _L, _I, _I, _I, _P, _P]),
     'se_mask_fwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P]),
     'se_mask_bwd': (C.c_int, [_I] + [_P, _L, _L] * 4 + [_L, _I, _L, _P, _P, _P, _P, _P, _P]),
     'se_polar_to_rect': (C.c_int, [_P, _P, _L, _I, _L, _P, _P]),
     'se_stft_fft_supported': (C.c_int, [_I, _I, _I]),
     'se_stft_fft_fwd': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _I, _P, _L, _P]),
     'se_istft_fft_fwd': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _P, _L, _L, _P, _P]),
+    'se_stft_fft_fwd_pcm16': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _I, _P, _L, _P]),
+    'se_istft_fft_fwd_pcm16': (C.c_int, [_P, _L, _L, _P, _I, _I, _I, _P, _L, _L, _P, _P]),
+    'se_pcm16_to_f32': (C.c_int, [_P, _L, _P, _P]),
+    'se_pcm16_from_f32': (C.c_int, [_P, _L, _P, _P]),
 }
 
 
@@ -81,7 +90,8 @@ class ConvArgs(C.Structure):
                 ('y_cl2', C.c_void_p), ('y_Cp', C.c_int),
                 ('y_bs', C.c_int64), ('y_cs', C.c_int64), ('y_hs', C.c_int64), ('y_ws', C.c_int64),
                 ('y_off', C.c_int64), ('y_lim', C.c_int64), ('y_scale', C.c_void_p),
-                ('src_H', C.c_int * 2), ('src_W', C.c_int * 2), ('src_C', C.c_int * 2)]
+                ('src_H', C.c_int * 2), ('src_W', C.c_int * 2), ('src_C', C.c_int * 2),
+                ('fold_h', C.c_int), ('fold_w', C.c_int), ('fold_cg', C.c_int), ('fold_cout2', C.c_int)]
 
 
 _lib = None

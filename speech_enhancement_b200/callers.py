@@ -66,6 +66,12 @@ def _fusable(model, x, first_block):
             and type(getattr(first_block, name)).__module__.startswith('speech_enhancement_b200'))
 
 
+def _clamped(wav):
+    """the models' final clamp_(-1, 1) (_2008_00264_dccrn.py:184); already done by the iSTFT epilogue when it wrote
+    PCM16 samples (ConviSTFT.pcm16_out)"""
+    return wav if wav.dtype == torch.int16 else torch.clamp_(wav, -1, 1)
+
+
 def _spec_planes(spec, n_bins):
     return spec[:, :n_bins, :], spec[:, n_bins:, :]
 
@@ -176,7 +182,7 @@ class DCCRN(nn.Module):
             mask_real, mask_imag = mask_real[..., :-1], mask_imag[..., :-1]
         est_spec = self._ops.mask_dccrn(self.masking, noisy_real, noisy_imag, mask_real, mask_imag)
         wav = self.istft(est_spec)
-        return est_spec, torch.clamp_(wav, -1, 1)
+        return est_spec, _clamped(wav)
 
     def forward(self, x):
         if self._use_fused(x):
@@ -203,7 +209,7 @@ class DCCRN(nn.Module):
             mask_real, mask_imag = mask_real[..., :-1], mask_imag[..., :-1]
         est_spec = self._ops.mask_dccrn(self.masking, noisy_real, noisy_imag, mask_real, mask_imag)
         wav = self.istft(est_spec)
-        return est_spec, torch.clamp_(wav, -1, 1)
+        return est_spec, _clamped(wav)
 
 
 # ------------------------------------------------------------------------------------ DCUNet
@@ -301,7 +307,7 @@ class DCUNet(nn.Module):
         real, imag = _spec_planes(spec, n_bins)
         est_spec = self._ops.mask_dcunet('bounded_tanh', real, imag, y[:, 0], y[:, 1])
         wav = self.istft(est_spec)
-        return est_spec, torch.clamp_(wav, -1, 1)
+        return est_spec, _clamped(wav)
 
     def forward(self, x):
         if _fusable(self, x, self.first_conv):
@@ -327,7 +333,7 @@ class DCUNet(nn.Module):
         x = x[:, :, :cs.shape[2], :cs.shape[3]]                           # dcunet.py:141-146
         est_spec = self._ops.mask_dcunet('bounded_tanh', cs[:, 0], cs[:, 1], x[:, 0], x[:, 1])
         wav = self.istft(est_spec)
-        return est_spec, torch.clamp_(wav, -1, 1)
+        return est_spec, _clamped(wav)
 
 
 # ------------------------------------------------------------------------------------ FRCRN
@@ -532,7 +538,7 @@ class FRCRN(nn.Module):
         _, y = self._final_block()([act], out_cl2=False, out_nchw=True)   # [B, 2, F-2, T]
         est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, y[:, 0], y[:, 1])
         wav = self.istft(est_spec)
-        return est_spec, torch.clamp_(wav, -1, 1)
+        return est_spec, _clamped(wav)
 
     def forward(self, x):
         if _fusable(self, x, self.encoder.layers[0]):
@@ -560,7 +566,7 @@ class FRCRN(nn.Module):
             x = self.final_conv(x)                                        # [B, 2, F-2, T]
         est_spec = self._ops.mask_frcrn(noisy_real, noisy_imag, x[:, 0], x[:, 1])
         wav = self.istft(est_spec)
-        return est_spec, torch.clamp_(wav, -1, 1)
+        return est_spec, _clamped(wav)
 
 
 # ------------------------------------------------------------------------------------ CARN

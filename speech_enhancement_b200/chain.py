@@ -130,7 +130,42 @@ def concat_channel_map(src_channels, mode):
     return [v for m in maps for v in m]
 
 
+def _phase_offsets(k, s, p):
+    """{phase r: [(tap d, input offset e)]}: output index s*q + r reads input index q + e through kernel tap d"""
+    return {r: [(d, (r + p - d) // s) for d in range(k) if (r + p - d) % s == 0] for r in range(s)}
+
+
+def _mma_cost(n):
+    """cycles of the split-operand MMAs of one 16-channel k-step at N accumulator columns (scripts/mma_rate.cu:
+    a 128 x N x 16 MMA costs max(N / 2, 84); concat form a_hi x [b_hi | b_lo] + a_lo x b_hi up to N = 128, three
+    N-wide MMAs beyond)"""
+    return max(n, 84) + max(n / 2, 84) if n <= 128 else 3 * max(n / 2, 84)
+
+
+def fold_transposed_weight(p4, sh, sw, fold):
+    """packed transposed-conv operand [Cout2, Cin2, kh, kw] (tap (dh, dw) takes input pixel (hi, wi) to output pixel
+    (hi*sh - ph + dh, wi*sw - pw + dw)) -> the operand of the equivalent stride-1 FORWARD convolution over the input
+    grid, [phases * cg, Cin2, n_e, n_f]: row (r*sw + s)*cg + co holds, at input offset (e, f), the tap through which
+    output phase (r, s) reads input pixel (q + e, p + f); zero where the phase has no such tap."""
+    es, fs, cg, nph = fold['es'], fold['fs'], fold['cg'], fold['nph']
+    cout2, cin2 = p4.shape[0], p4.shape[1]
+    wf = torch.zeros((nph * cg, cin2, len(es), len(fs)), device=p4.device, dtype=p4.dtype)
+    for r in range(sh):
+        for sph in range(sw):
+            c0 = (r * sw + sph) * cg
+            for dh, e in fold['oh'][r]:
+                for dw, fo in fold['ow'][sph]:
+                    wf[c0:c0 + cout2, :, e - es[0], fo - fs[0]] = p4[:, :, dh, dw]
+    return wf
+
+
+# SE_CONV_FOLD: 'auto' (fold where the MMA cost model says it pays), '0' never, '1' wherever the shape allows
+FOLD_MODE = os.environ.get('SE_CONV_FOLD', 'auto')
+
+
 class FusedBlock:
+    fold = None                 # phase-folding plan of a transposed layer (set in __init__ where it applies)
+
     """conv / convT (+ eval-mode complex BN) (+ leaky activation) of one reference block, prepared for
     the chained engine.  `conv` is a ComplexConv2d / ComplexConvTranspose2d of this package."""
 
@@ -154,6 +189,25 @@ class FusedBlock:
         # transposed layers with 2 or 4 output channels run in scatter form (1x1 GEMM over the taps + gather):
         # one pass over the input instead of one >= 84-cycle MMA per tap for a handful of useful columns
         self.scatter_form = self.transposed and self.cout2 in (2, 4) and self.kh * self.kw * self.cout2 <= 128
+        # transposed layers with few output channels and stride > 1 run PHASE-FOLDED: the sh*sw output phases read the
+        # same input tile through different taps, so they become column groups of ONE stride-1 convolution over the
+        # input grid (n_e x n_f input offsets instead of kh x kw taps, N = phases * channels instead of channels);
+        # every MMA pays the 128-row A-operand read (>= 84 cycles) however narrow N is, so fewer, wider MMAs win
+        self.fold = None
+        if self.transposed and not self.scatter_form and self.sh * self.sw > 1 and FOLD_MODE != '0':
+            oh, ow = _phase_offsets(self.kh, self.sh, self.ph), _phase_offsets(self.kw, self.sw, self.pw)
+            es = sorted({e for v in oh.values() for _, e in v})
+            fs = sorted({f for v in ow.values() for _, f in v})
+            cg = (self.cout2 + 31) // 32 * 32
+            nph = self.sh * self.sw
+            if es and fs and nph * cg <= 256 and len(es) * len(fs) <= 49:
+                # 'auto' keeps to the concat operand form (<= 128 folded columns): measured on DCUNet dec7 (4 phases x
+                # 64 = 256 columns, split form) the folded launch LOSES, 6.97 -> 9.98 ms, although the MMA model favours it
+                es, fs = list(range(es[0], es[-1] + 1)), list(range(fs[0], fs[-1] + 1))   # contiguous offset window
+                gain = (self.kh * self.kw * _mma_cost((self.cout2 + 15) // 16 * 16)
+                        / (len(es) * len(fs) * _mma_cost(nph * cg)))
+                if FOLD_MODE == '1' or (gain > 1.1 and nph * cg <= 128):
+                    self.fold = dict(oh=oh, ow=ow, es=es, fs=fs, cg=cg, nph=nph, gain=gain)
         self._key = None
         self._ops = None
 
@@ -207,7 +261,22 @@ class FusedBlock:
                 with torch.cuda.device(dev):
                     _abi.check(lib.se_cconv_prep_weight(_abi.ptr(p3), taps * 2 * co, 2 * ci, 1, _abi.ptr(cmap_t), cpt,
                                                         _abi.ptr(wq_sc), _abi.stream_ptr()))
-        self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt, 'wq_sc': wq_sc}
+            wq_fold = bias_fold = None
+            if self.fold is not None:
+                f = self.fold
+                es, fs, cg, nph = f['es'], f['fs'], f['cg'], f['nph']
+                wf = fold_transposed_weight(packed.view(2 * co, 2 * ci, kh, kw), self.sh, self.sw, f)
+                wf = wf.reshape(nph * cg, 2 * ci * len(es) * len(fs)).contiguous()
+                bias_fold = torch.zeros((nph, cg), device=dev, dtype=torch.float32)
+                bias_fold[:, :2 * co] = bias
+                bias_fold = bias_fold.reshape(-1).contiguous()
+                ntap = len(es) * len(fs)
+                wq_fold = torch.empty((lib.se_cconv_wq_elems(nph * cg, cpt, ntap),), device=dev, dtype=torch.bfloat16)
+                with torch.cuda.device(dev):
+                    _abi.check(lib.se_cconv_prep_weight(_abi.ptr(wf), nph * cg, 2 * ci, ntap, _abi.ptr(cmap_t), cpt,
+                                                        _abi.ptr(wq_fold), _abi.stream_ptr()))
+        self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt, 'wq_sc': wq_sc,
+                     'wq_fold': wq_fold, 'bias_fold': bias_fold}
         self._key = key
         return self._ops
 
@@ -279,6 +348,14 @@ class FusedBlock:
                                                 self.ph, self.pw, Ho, Wo, _abi.ptr(ops['bias']), ops['slope'],
                                                 _abi.ptr(y), _abi.stream_ptr()))
             return None, y
+        if self.fold is not None and y is None and y_act is not None:
+            # phase-folded form: stride-1 forward convolution over the input grid, phases as column groups
+            f = self.fold
+            a.transposed, a.kh, a.kw, a.sh, a.sw = 0, len(f['es']), len(f['fs']), 1, 1
+            a.ph, a.pw = -f['es'][0], -f['fs'][0]
+            a.Cout2 = f['nph'] * f['cg']
+            a.fold_h, a.fold_w, a.fold_cg, a.fold_cout2 = self.sh, self.sw, f['cg'], self.cout2
+            a.wq, a.bias = ops['wq_fold'].data_ptr(), ops['bias_fold'].data_ptr()
         with torch.cuda.device(dev), _abi.stage('cconv'):
             _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
         return y_act, y

@@ -239,9 +239,15 @@ class ConvSTFT(_abi.InvalidatesCaches, nn.Module):
         window = w[0, 0]                                  # row f = 0 of the real block is the analysis window
         eng = self._pick_engine('ConvSTFT', window, False, B > 0)
         with torch.cuda.device(x.device), _abi.stage('stft'):
+            if x.dtype == torch.int16 and eng != 'fft':
+                # framings outside the FFT engine: one conversion pass, then the fp32 engines
+                xf = torch.empty(x.shape, device=x.device, dtype=torch.float32)
+                _abi.check(_abi.lib().se_pcm16_to_f32(_abi.ptr(x), x.numel(), _abi.ptr(xf), _abi.stream_ptr()))
+                x = xf
             if eng == 'fft':
-                _abi.check(_abi.lib().se_stft_fft_fwd(_abi.ptr(x), B, L, _abi.ptr(window), win, self.hop_size,
-                                                      self.fft_size, pad, _abi.ptr(out), T, _abi.stream_ptr()))
+                fn = _abi.lib().se_stft_fft_fwd_pcm16 if x.dtype == torch.int16 else _abi.lib().se_stft_fft_fwd
+                _abi.check(fn(_abi.ptr(x), B, L, _abi.ptr(window), win, self.hop_size,
+                              self.fft_size, pad, _abi.ptr(out), T, _abi.stream_ptr()))
             elif eng == 'umma':
                 _frames_project(x, self._cached('fwd', _frames_operand), self.hop_size, pad, T, out)
             else:
@@ -273,7 +279,15 @@ class ConvSTFT(_abi.InvalidatesCaches, nn.Module):
         return gx
 
     def forward(self, inputs):
-        x = _abi.require_cuda_f32(inputs, 'ConvSTFT.forward(inputs)')
+        """inputs: fp32 waveform [L] / [B, L] / [B, 1, L] (conv_stft.py:48-52), or the same shapes in int16: PCM_S 16
+        samples as they sit in the wav file (audio_dataset.py:12-21), scaled by 1 / 32768 in the kernel's stage load."""
+        if torch.is_tensor(inputs) and inputs.dtype == torch.int16:
+            if not inputs.is_cuda:
+                raise RuntimeError('ConvSTFT.forward(inputs): speech_enhancement_b200 runs on CUDA (sm_100a) only; got a '
+                                   'cpu tensor and there is no CPU fallback')
+            x = inputs
+        else:
+            x = _abi.require_cuda_f32(inputs, 'ConvSTFT.forward(inputs)')
         if x.dim() == 1:
             x = x[None, :]
         elif x.dim() == 3:
@@ -329,6 +343,10 @@ class ConviSTFT(_abi.InvalidatesCaches, nn.Module):
         self._scale = {}
 
     engine = 'auto'
+    # True: forward returns int16 PCM_S 16 samples -- clamp(-1, 1) (the models' final clamp_, _2008_00264_dccrn.py:184),
+    # round to nearest, saturate -- written by the overlap-add epilogue itself (inference only).  The chained forwards
+    # (callers.py / dropin.accelerate) skip their clamp_ when they see an int16 waveform.
+    pcm16_out = False
 
     _cached = ConvSTFT._cached
     _fft_ready = ConvSTFT._fft_ready
@@ -354,14 +372,16 @@ class ConviSTFT(_abi.InvalidatesCaches, nn.Module):
         w = self.weight
         c2, _, win = w.shape
         B, _, T = spec.shape
-        out = torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
         eng = self._pick_engine('ConviSTFT', self.window, True)
+        fused_pcm = self.pcm16_out and eng == 'fft'
+        out = torch.empty((B, out_len), device=spec.device, dtype=torch.int16 if fused_pcm else torch.float32)
         with torch.cuda.device(spec.device), _abi.stage('istft'):
             if eng == 'fft':
                 J = -(-win // self.hop_size)
-                _abi.check(_abi.lib().se_istft_fft_fwd(_abi.ptr(spec), B, T, _abi.ptr(self.window), win, self.hop_size,
-                                                       self.fft_size, _abi.ptr(self._ola_scale(T, J)), start, out_len,
-                                                       _abi.ptr(out), _abi.stream_ptr()))
+                fn = _abi.lib().se_istft_fft_fwd_pcm16 if fused_pcm else _abi.lib().se_istft_fft_fwd
+                _abi.check(fn(_abi.ptr(spec), B, T, _abi.ptr(self.window), win, self.hop_size,
+                              self.fft_size, _abi.ptr(self._ola_scale(T, J)), start, out_len,
+                              _abi.ptr(out), _abi.stream_ptr()))
             elif eng == 'umma':
                 operand = self._cached('fwd', _ola_operand)
                 _overlap_add(spec, operand, self.hop_size, self._ola_scale(T, operand[0]), out, start, out_len)
@@ -371,6 +391,10 @@ class ConviSTFT(_abi.InvalidatesCaches, nn.Module):
                 _abi.check(_abi.lib().se_istft_fwd(_abi.ptr(spec), None, _abi.ptr(packed), _abi.ptr(window), B, c2, T,
                                                    win, self.hop_size, start, out_len, _abi.ptr(out),
                                                    _abi.stream_ptr()))
+            if self.pcm16_out and not fused_pcm:
+                pcm = torch.empty((B, out_len), device=spec.device, dtype=torch.int16)
+                _abi.check(_abi.lib().se_pcm16_from_f32(_abi.ptr(out), out.numel(), _abi.ptr(pcm), _abi.stream_ptr()))
+                out = pcm
         return out
 
     def _synthesize_adjoint(self, g, T, start):
@@ -438,7 +462,10 @@ class ConviSTFT(_abi.InvalidatesCaches, nn.Module):
             end = min(end, start + output_length)
         out_len = max(end - start, 0)
         if out_len == 0 or B == 0:
-            return torch.empty((B, out_len), device=spec.device, dtype=torch.float32)
+            return torch.empty((B, out_len), device=spec.device,
+                               dtype=torch.int16 if self.pcm16_out and not needs_grad else torch.float32)
         if needs_grad:
+            if self.pcm16_out:
+                raise RuntimeError('ConviSTFT: pcm16_out is an inference option (int16 samples carry no gradient)')
             return _IstftFn.apply(self, spec, start, out_len)
         return self._synthesize(spec, start, out_len)

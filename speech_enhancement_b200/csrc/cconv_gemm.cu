@@ -55,6 +55,11 @@ struct GemmParams {
   int a_half, a_slot, b_unit, SA, SB;
   int ntiles, nbuf, buf_cols;  // persistent tile loop; nbuf TMEM accumulator buffers of buf_cols columns
   int Ho, Wo, Cout2, npad, tmem_cols, y_Cp;
+  // phase folding (transposed convolution as ONE stride-1 convolution whose accumulator columns are the sh*sw output
+  // phases side by side): column group ph = r * fold_w + s of quotient pixel (qh, qw) is output pixel
+  // (qh * fold_h + r, qw * fold_w + s).  Cg = accumulator columns per phase, Cout2g = real channels per phase.
+  // Not folded: fold_h = fold_w = 1, Cg = npad, Cout2g = Cout2.
+  int fold_h, fold_w, Cg, Cout2g;
   const float* bias;
   float slope;
   float* y;
@@ -394,12 +399,14 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
     const int m = q * 32 + lane;
     const int hl = m / p.TW, wl = m - hl * p.TW;
     const int64_t plane = (int64_t)p.Ho * p.Wo;
-    const int cmax = p.y_cl2 != nullptr && p.y_Cp > p.npad ? p.y_Cp : p.npad;
     const bool do_f32 = p.y != nullptr, do_cl2 = p.y_cl2 != nullptr;
     const bool checked = p.y_lim != 0 || p.y_scale != nullptr;
     const bool act = p.slope != 1.f;
     const float slope = p.slope;
     const int64_t lo_off = plane * p.y_Cp;
+    const int nph = p.fold_h * p.fold_w, Cg = p.Cg;
+    // 32-column chunks per phase: the accumulator columns, then (CL2 output only) the zero pad channels up to y_Cp
+    const int cpp = ((do_cl2 && p.y_Cp > Cg ? p.y_Cp : Cg) + 31) >> 5;
     uint32_t lt = 0;
     const bool prof = p.prof != nullptr;
     unsigned long long w_f = 0;
@@ -414,20 +421,36 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
       const int64_t b = tc.b;
       for (int a = 0; a < tc.nacc; ++a) {
         const int qh = tc.h0 + a * p.TH + hl, qw = tc.w0 + wl;
-        const int ho = qh * C.oh_mul + C.oh_add, wo = qw * C.ow_mul + C.ow_add;
-        const bool ok = qh < C.Hq_out && qw < C.Wq_out && ho < p.Ho && wo < p.Wo;
-        const int64_t ypos = (int64_t)wo * p.y_ws;           // + co * y_cs: position inside the (b, ho) row block
+        const bool q_ok = qh < C.Hq_out && qw < C.Wq_out;
+        const int ho0 = qh * C.oh_mul + C.oh_add, wo0 = qw * C.ow_mul + C.ow_add;
+        const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.buf_cols + (uint32_t)(a * p.acc_cols);
+        // output coordinates of phase 0 (the only phase unless the launch is folded)
+        int ho = ho0, wo = wo0;
+        bool ok = q_ok && ho < p.Ho && wo < p.Wo;
+        int64_t ypos = (int64_t)wo * p.y_ws;                 // + co * y_cs: position inside the (b, ho) row block
         float* yb = do_f32 ? p.y + b * p.y_bs + (int64_t)ho * p.y_hs + p.y_off + ypos : nullptr;
         __nv_bfloat16* cb = do_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
-        const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.buf_cols + (uint32_t)(a * p.acc_cols);
-        for (int c0 = chalf * 32; c0 < cmax; c0 += 64) {
+        for (int g = chalf; g < nph * cpp; g += 2) {
+          int cc = g << 5, tcol = cc;                        // channel offset inside the phase, accumulator column
+          if (nph > 1) {
+            const int ph = g / cpp;
+            cc = (g - ph * cpp) << 5;
+            tcol = ph * Cg + cc;
+            const int r = ph / p.fold_w;
+            ho = ho0 + r; wo = wo0 + (ph - r * p.fold_w);
+            ok = q_ok && ho < p.Ho && wo < p.Wo;
+            ypos = (int64_t)wo * p.y_ws;
+            yb = do_f32 ? p.y + b * p.y_bs + (int64_t)ho * p.y_hs + p.y_off + ypos : nullptr;
+            cb = do_cl2 ? p.y_cl2 + (b * 2 * plane + (int64_t)ho * p.Wo + wo) * p.y_Cp : nullptr;
+          }
+          const int c0 = cc;
           float v[32];
-          if (have && c0 < p.npad) {
+          if (have && cc < Cg) {
             uint32_t r[32];
-            ptx::tmem_ld_32x32(trow + (uint32_t)c0, r);
+            ptx::tmem_ld_32x32(trow + (uint32_t)tcol, r);
             if (kConcat) {
               uint32_t r2[32];
-              ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + c0), r2);
+              ptx::tmem_ld_32x32(trow + (uint32_t)(p.npad + tcol), r2);
               ptx::tmem_ld_wait();
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]);
@@ -436,13 +459,19 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
             }
+            if (cc + 32 > Cg) {
+              // accumulator width is a multiple of 16, chunks are 32 wide: the upper half of the last chunk is not
+              // part of this accumulator -- those columns are pad channels of the output and must read as zero
+#pragma unroll
+              for (int j = 16; j < 32; ++j) v[j] = 0.f;
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = 0.f;
           }
           if (!ok) continue;
-          {
-            const float4* b4 = reinterpret_cast<const float4*>(s_bias + c0);
+          if (cc < Cg) {
+            const float4* b4 = reinterpret_cast<const float4*>(s_bias + tcol);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 bb = b4[j];
@@ -453,8 +482,8 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f) + slope * fminf(v[j], 0.f);
           }
-          if (do_f32 && c0 < p.Cout2) {
-            const int nv = p.Cout2 - c0;                      // valid columns in this chunk (may exceed 32)
+          if (do_f32 && c0 < p.Cout2g) {
+            const int nv = p.Cout2g - c0;                     // valid columns in this chunk (may exceed 32)
             if (p.y_vec4 == 2) {
               // 256-bit stores: a whole 32-byte sector per lane and instruction (lanes are a row apart)
 #pragma unroll
@@ -587,7 +616,10 @@ static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max)
         c.Hq_out = (a->Ho - ch + a->sh - 1) / a->sh; c.Wq_out = (a->Wo - cw + a->sw - 1) / a->sw;
         c.oh_mul = a->sh; c.oh_add = ch; c.ow_mul = a->sw; c.ow_add = cw;
       } else {
-        c.Hq_out = a->Ho; c.Wq_out = a->Wo; c.oh_mul = 1; c.oh_add = 0; c.ow_mul = 1; c.ow_add = 0;
+        // folded launch: the M dimension walks the quotient grid, the column groups are the output phases
+        const int fh = a->fold_h > 1 ? a->fold_h : 1, fw = a->fold_w > 1 ? a->fold_w : 1;
+        c.Hq_out = (a->Ho + fh - 1) / fh; c.Wq_out = (a->Wo + fw - 1) / fw;
+        c.oh_mul = fh; c.oh_add = 0; c.ow_mul = fw; c.ow_add = 0;
       }
       if (c.Hq_out <= 0 || c.Wq_out <= 0) continue;
       c.g0 = ng; c.ng = 0;
@@ -750,6 +782,13 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   if (a->B > 32767) return fail(SE_ERR_UNSUPPORTED, "%s: batch too large", nm);
   if (a->transposed && (a->pad_top || a->pad_left))
     return fail(SE_ERR_UNSUPPORTED, "%s: pad_top/pad_left only for the forward convolution", nm);
+  if (a->fold_h > 1 || a->fold_w > 1) {
+    const int nph = (a->fold_h > 1 ? a->fold_h : 1) * (a->fold_w > 1 ? a->fold_w : 1);
+    if (a->transposed || a->sh != 1 || a->sw != 1 || a->fold_cg <= 0 || a->fold_cg % 32 != 0 ||
+        a->Cout2 != nph * a->fold_cg || a->fold_cout2 <= 0 || a->fold_cout2 > a->fold_cg)
+      return fail(SE_ERR_BAD_ARG, "%s: a folded launch is a stride-1 forward convolution with Cout2 = phases * fold_cg "
+                                  "columns, fold_cg a multiple of 32 and fold_cout2 <= fold_cg", nm);
+  }
   for (int i = 0; i < a->nsrc; ++i)
     if (a->src_Cp[i] <= 0 || a->src_Cp[i] % 64 != 0)
       return fail(SE_ERR_BAD_ARG, "%s: source channel pitch must be a positive multiple of 64", nm);
@@ -786,6 +825,10 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   p.b_unit = p.unit_rows * 128;
   p.SA = tc.SA; p.SB = tc.SB;
   p.Ho = a->Ho; p.Wo = a->Wo; p.Cout2 = a->Cout2; p.npad = npad; p.y_Cp = a->y_Cp;
+  const bool folded = a->fold_h > 1 || a->fold_w > 1;
+  p.fold_h = a->fold_h > 1 ? a->fold_h : 1; p.fold_w = a->fold_w > 1 ? a->fold_w : 1;
+  p.Cg = folded ? a->fold_cg : npad;
+  p.Cout2g = folded ? a->fold_cout2 : a->Cout2;
   // TMEM: nacc accumulators per buffer; two buffers when they fit (epilogue overlaps the next tile's MMAs)
   const int tm_one = (tc.nacc - 1) * p.acc_cols + (concat ? npad : 0) + round_up(npad, 32);
   p.buf_cols = round_up(tc.nacc * p.acc_cols, 32);
@@ -948,7 +991,8 @@ extern "C" int se_cconv_gemm(const se_cconv_args* a, void* stream) {
   SE_REQUIRE(a->y_nchw || a->y_cl2, "se_cconv_gemm: no output requested");
   SE_REQUIRE(a->B >= 0 && a->H > 0 && a->W > 0 && a->Cout2 > 0 && a->kh > 0 && a->kw > 0 && a->sh > 0 &&
              a->sw > 0 && a->Ho > 0 && a->Wo > 0, "se_cconv_gemm: bad geometry");
-  SE_REQUIRE(a->y_cl2 == nullptr || (a->y_Cp >= a->Cout2 && a->y_Cp % 64 == 0),
+  SE_REQUIRE(a->y_cl2 == nullptr ||
+             (a->y_Cp >= ((a->fold_h > 1 || a->fold_w > 1) ? a->fold_cout2 : a->Cout2) && a->y_Cp % 64 == 0),
              "se_cconv_gemm: y_Cp must be a multiple of 64 >= Cout2");
   for (int i = 0; i < a->nsrc; ++i)
   {

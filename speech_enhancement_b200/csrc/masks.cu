@@ -143,18 +143,18 @@ __device__ __forceinline__ void mask_grad(float nr, float ni, float mr, float mi
   }
 }
 
-// grid: (ceil(T / blockDim), rows = B*F); outputs contiguous: dn_* [B,F,T], dm_* [B,Fm,T]
+// grid: (ceil(T / blockDim), min(rows = B*F, 65535)), rows strided over grid.y; outputs contiguous: dn_* [B,F,T], dm_* [B,Fm,T]
 template <int KIND>
 __global__ void __launch_bounds__(128)
-mask_bwd_kernel(Plane nr, Plane ni, Plane mr, Plane mi, int F, int64_t T, const float* __restrict__ g,
+mask_bwd_kernel(Plane nr, Plane ni, Plane mr, Plane mi, int64_t rows, int F, int64_t T, const float* __restrict__ g,
                 float* __restrict__ dnr, float* __restrict__ dni, float* __restrict__ dmr, float* __restrict__ dmi) {
-  const int64_t row = blockIdx.y;
-  const int64_t b = row / F; const int f = (int)(row - b * F);
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= T) return;
   const int Fm = KIND == SE_MASK_FRCRN ? F - 2 : F;
+  for (int64_t row = blockIdx.y; row < rows; row += gridDim.y) {
+  const int64_t b = row / F; const int f = (int)(row - b * F);
   const int64_t on = (b * F + f) * T + t;
-  if (KIND == SE_MASK_FRCRN && f < 2) { dnr[on] = 0.f; dni[on] = 0.f; return; }
+  if (KIND == SE_MASK_FRCRN && f < 2) { dnr[on] = 0.f; dni[on] = 0.f; continue; }
   const int fm = KIND == SE_MASK_FRCRN ? f - 2 : f;
   const float a = __ldg(nr.p + b * nr.bs + f * nr.fs + t), c = __ldg(ni.p + b * ni.bs + f * ni.fs + t);
   const float d = __ldg(mr.p + b * mr.bs + fm * mr.fs + t), e = __ldg(mi.p + b * mi.bs + fm * mi.fs + t);
@@ -164,15 +164,15 @@ mask_bwd_kernel(Plane nr, Plane ni, Plane mr, Plane mi, int F, int64_t T, const 
   dnr[on] = o0; dni[on] = o1;
   const int64_t om = (b * Fm + fm) * T + t;
   dmr[om] = o2; dmi[om] = o3;
+  }
 }
 
 template <int KIND>
 int launch_mask_bwd(Plane nr, Plane ni, Plane mr, Plane mi, int64_t B, int F, int64_t T, const float* g, float* dnr,
                     float* dni, float* dmr, float* dmi, cudaStream_t s) {
   const int64_t rows = B * F;
-  if (rows > 65535) return fail(SE_ERR_UNSUPPORTED, "se_mask_bwd: B*F > 65535 (split the batch)");
-  dim3 grid((unsigned)((T + 127) / 128), (unsigned)rows);
-  mask_bwd_kernel<KIND><<<grid, 128, 0, s>>>(nr, ni, mr, mi, F, T, g, dnr, dni, dmr, dmi);
+  dim3 grid((unsigned)((T + 127) / 128), (unsigned)(rows < 65535 ? rows : 65535));    // rows beyond grid.y are looped
+  mask_bwd_kernel<KIND><<<grid, 128, 0, s>>>(nr, ni, mr, mi, rows, F, T, g, dnr, dni, dmr, dmi);
   return check_launch("se_mask_bwd");
 }
 
@@ -231,4 +231,35 @@ extern "C" int se_mask_bwd(int kind,
   }
 #undef SE_BWD
   return se::fail(SE_ERR_BAD_ARG, "se_mask_bwd: unknown kind %d", kind);
+}
+
+// ---- PCM_S 16 <-> fp32 (the wire format of audio_dataset.py:12-21 / mix_audio.py:144-146) ----------
+// For the framings the FFT engine does not cover: the fused forms live in stft_fft.cu (se_stft_fft_fwd_pcm16 /
+// se_istft_fft_fwd_pcm16).  from_f32 applies the models' clamp(-1, 1) and FFmpeg's flt -> s16 rule
+// av_clip_int16(lrintf(x * 2^15)) (what torchaudio.save(encoding="PCM_S", bits_per_sample=16) runs); to_f32 is
+// torchaudio.load's x / 32768.
+namespace se {
+__global__ void __launch_bounds__(256) pcm16_to_f32_kernel(const int16_t* __restrict__ x, float* __restrict__ y, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] = (float)__ldg(x + i) * (1.0f / 32768.0f);
+}
+__global__ void __launch_bounds__(256) pcm16_from_f32_kernel(const float* __restrict__ x, int16_t* __restrict__ y, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = fminf(fmaxf(__ldg(x + i), -1.0f), 1.0f);
+    y[i] = (int16_t)min(__float2int_rn(v * 32768.0f), 32767);
+  }
+}
+}  // namespace se
+
+extern "C" int se_pcm16_to_f32(const int16_t* x, int64_t n, float* y, void* stream) {
+  SE_REQUIRE(x && y && n >= 0, "se_pcm16_to_f32: bad arguments");
+  if (n == 0) return SE_OK;
+  se::pcm16_to_f32_kernel<<<se::grid_1d(n), 256, 0, (cudaStream_t)stream>>>(x, y, n);
+  return se::check_launch("se_pcm16_to_f32");
+}
+extern "C" int se_pcm16_from_f32(const float* x, int64_t n, int16_t* y, void* stream) {
+  SE_REQUIRE(x && y && n >= 0, "se_pcm16_from_f32: bad arguments");
+  if (n == 0) return SE_OK;
+  se::pcm16_from_f32_kernel<<<se::grid_1d(n), 256, 0, (cudaStream_t)stream>>>(x, y, n);
+  return se::check_launch("se_pcm16_from_f32");
 }

@@ -16,6 +16,7 @@
 // part): 16 points per lane, radix-16 in registers, one transpose through shared memory, radix-16 in registers
 // again and a final radix-2 across lane pairs (shfl.xor 16).  Spectra / frames of the whole tile are staged in
 // shared memory so that every global access is a contiguous run along the frame axis.
+#include <type_traits>
 #include <utility>
 #include "common.cuh"
 #include "umma.cuh"
@@ -205,8 +206,12 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // out[b, f, t] = Re X_t[f], out[b, F + f, t] = Im X_t[f],  X_t = rfft_N( window * reflect_pad(x)[t*hop : t*hop + win] )
 // Persistent CTAs walk the (utterance, tile of 32 frames) list; the next tile's samples stream into the other half of
 // a double buffer while this tile is transformed.
+// TIn = float, or int16_t for PCM16 clips (the wav files of audio_dataset.py:12-21 are PCM_S 16;
+// torchaudio.load scales by 1 / 32768): the int16 -> fp32 conversion happens in this stage load, so a PCM clip costs
+// 2 bytes per sample of HBM read instead of a separate conversion pass (2 read + 4 written + 4 read).
+template <typename TIn>
 __global__ void __launch_bounds__(FTHREADS, 2)
-stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict__ window, int win, int hop, int pad,
+stft_fft_kernel(const TIn* __restrict__ x, int64_t L, const float* __restrict__ window, int win, int hop, int pad,
                 float* __restrict__ out, int T, int tiles, int total, int xs_cap) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* zbuf = reinterpret_cast<float2*>(smem_raw);                   // [TILE/2][ZPITCH]
@@ -233,9 +238,18 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
     const int nfr = min(TILE, T - t0);
     const int nsamp = (nfr - 1) * hop + win;
     const int64_t s0 = (int64_t)t0 * hop - pad;
-    const float* xb = x + (int64_t)b * L;
-    if (s0 >= 0 && s0 + nsamp <= L && ((reinterpret_cast<uintptr_t>(xb + s0) & 15) == 0)) {
-      const float* src = xb + s0;
+    const TIn* xb = x + (int64_t)b * L;
+    if constexpr (!std::is_same<TIn, float>::value) {
+      // PCM16: plain loads with the reflect mirror, converted on the way into shared memory
+      for (int i = tid; i < nsamp; i += FTHREADS) {
+        int64_t sidx = s0 + i;
+        if (sidx < 0) sidx = -sidx;
+        else if (sidx >= L) sidx = 2 * (L - 1) - sidx;
+        dst[i] = (float)__ldg(xb + sidx) * (1.0f / 32768.0f);
+      }
+      if (tid == 0) ptx::mbar_arrive(bar);
+    } else if (s0 >= 0 && s0 + nsamp <= L && ((reinterpret_cast<uintptr_t>(xb + s0) & 15) == 0)) {
+      const float* src = reinterpret_cast<const float*>(xb) + s0;
       const int n4 = nsamp & ~3;
       if (tid == 0) {
         ptx::fence_proxy_async_smem();         // the buffer was read through the generic proxy one tile ago
@@ -248,7 +262,7 @@ stft_fft_kernel(const float* __restrict__ x, int64_t L, const float* __restrict_
         int64_t sidx = s0 + i;
         if (sidx < 0) sidx = -sidx;
         else if (sidx >= L) sidx = 2 * (L - 1) - sidx;
-        cp_async4(dst + i, xb + sidx);
+        cp_async4(dst + i, reinterpret_cast<const float*>(xb) + sidx);
       }
       if (tid == 0) ptx::mbar_arrive(bar);
     }
@@ -337,9 +351,20 @@ constexpr int IPAIRS = TILE / 2;            // frame pairs per tile
 constexpr int IPITCH = 2 * (IPAIRS | 1);    // floats per spectrum row in shared memory; IPITCH / 2 odd
 
 // interior tiles: every frame exists, every tap is below `win`, every sample is inside the crop
-template <int JJ>
+// fp32 sample -> stored sample.  int16_t = PCM_S 16 as the reference's savers write it (mix_audio.py:144-146,
+// trainer.py:255-262: torchaudio.save(encoding="PCM_S", bits_per_sample=16), which in torchaudio >= 2.9 is FFmpeg's
+// flt -> s16 conversion av_clip_int16(lrintf(x * 2^15))), with the models' final clamp(-1, 1)
+// (_2008_00264_dccrn.py:184) fused in front of it.
+template <typename TOut> __device__ __forceinline__ TOut to_sample(float v);
+template <> __device__ __forceinline__ float to_sample<float>(float v) { return v; }
+template <> __device__ __forceinline__ int16_t to_sample<int16_t>(float v) {
+  v = fminf(fmaxf(v, -1.0f), 1.0f);
+  return (int16_t)min(__float2int_rn(v * 32768.0f), 32767);
+}
+
+template <int JJ, typename TOut>
 __device__ __forceinline__ void ola_interior(const float* sbuf, int total_s, int hop, int halo, unsigned hop_magic,
-                                             const float* __restrict__ scale, float* __restrict__ dst, int tid) {
+                                             const float* __restrict__ scale, TOut* __restrict__ dst, int tid) {
   const int jstep = hop * IPITCH - 1;
   for (int i = tid; i < total_s; i += THREADS) {
     int ql = __umulhi((unsigned)i, hop_magic);           // i / hop
@@ -347,14 +372,15 @@ __device__ __forceinline__ void ola_interior(const float* sbuf, int total_s, int
     float acc = col[0];
 #pragma unroll
     for (int j = 1; j < JJ; ++j) acc += col[j * jstep];
-    dst[i] = acc * __ldg(scale + i);
+    dst[i] = to_sample<TOut>(acc * __ldg(scale + i));
   }
 }
 
+template <typename TOut>
 __global__ void __launch_bounds__(THREADS, 2)
 istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict__ window, int win, int hop, int J,
                  float c_even, float c_odd, const float* __restrict__ scale, int64_t crop, int64_t out_len,
-                 float* __restrict__ out, int Q, int tq, int tiles, int total, unsigned hop_magic) {
+                 TOut* __restrict__ out, int Q, int tq, int tiles, int total, unsigned hop_magic) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int F = NFFT / 2 + 1, C2 = 2 * F;
   float* sbuf = reinterpret_cast<float*>(smem_raw);                         // [C2][IPITCH]: spectra, then frames
@@ -455,13 +481,13 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
     // overlap-add in a fixed order, normalise, crop:  sample n = q*hop + r sums frame q - j at offset j*hop + r.
     // Frames outside [0, T) are skipped, not added as zeros: the partner of a real frame in a pair carries that
     // frame's rounding noise, which the 1 / (window^2 + 1e-8) normaliser would amplify at un-centred clip edges.
-    float* ob = out + (int64_t)b * out_len;
+    TOut* ob = out + (int64_t)b * out_len;
     const int total_s = nq * hop;
     const int64_t n0 = (int64_t)q0 * hop;
     const bool interior = q0 - (J - 1) >= 0 && q0 + nq <= T && J * hop == win && n0 >= crop &&
                           n0 + total_s <= crop + out_len && scale != nullptr;
-    if (interior && J == 4) ola_interior<4>(sbuf, total_s, hop, halo, hop_magic, scale + n0, ob + (n0 - crop), tid);
-    else if (interior && J == 2) ola_interior<2>(sbuf, total_s, hop, halo, hop_magic, scale + n0, ob + (n0 - crop), tid);
+    if (interior && J == 4) ola_interior<4, TOut>(sbuf, total_s, hop, halo, hop_magic, scale + n0, ob + (n0 - crop), tid);
+    else if (interior && J == 2) ola_interior<2, TOut>(sbuf, total_s, hop, halo, hop_magic, scale + n0, ob + (n0 - crop), tid);
     else {
       for (int i = tid; i < total_s; i += THREADS) {
         int ql = __umulhi((unsigned)i, hop_magic), r = i - ql * hop;
@@ -471,7 +497,7 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
           if (m < win && t >= 0 && t < T) acc += sbuf[m * IPITCH + (ql - j + halo)];
         }
         int64_t n = n0 + i, pos = n - crop;
-        if (pos >= 0 && pos < out_len) ob[pos] = scale ? acc * __ldg(scale + n) : acc;
+        if (pos >= 0 && pos < out_len) ob[pos] = to_sample<TOut>(scale ? acc * __ldg(scale + n) : acc);
       }
     }
     __syncthreads();                         // the next tile restages sbuf
@@ -487,55 +513,59 @@ bool fft_framing_ok(int win, int hop, int fft) {
 
 extern "C" int se_stft_fft_supported(int win, int hop, int fft) { return se::fft_framing_ok(win, hop, fft) ? 1 : 0; }
 
-extern "C" int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
-                               int pad, float* out, int64_t T, void* stream) {
-  using namespace se;
-  SE_REQUIRE(x && window && out, "se_stft_fft_fwd: null pointer");
-  SE_REQUIRE(B >= 0 && L > 0 && T >= 0 && pad >= 0, "se_stft_fft_fwd: bad dims");
+namespace se {
+namespace {
+
+template <typename TIn>
+int stft_fft_launch(const char* nm, const TIn* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
+                    int pad, float* out, int64_t T, void* stream) {
+  SE_REQUIRE(x && window && out, "%s: null pointer", nm);
+  SE_REQUIRE(B >= 0 && L > 0 && T >= 0 && pad >= 0, "%s: bad dims", nm);
   if (!fft_framing_ok(win, hop, fft))
-    return fail(SE_ERR_UNSUPPORTED, "se_stft_fft_fwd: win %d / hop %d / fft %d outside the FFT engine (fft 512, hop <= 256, "
-                                    "ceil(win/hop) <= %d)", win, hop, fft, MAXJ);
-  SE_REQUIRE(pad < L && (T - 1) * hop + win <= L + 2 * (int64_t)pad, "se_stft_fft_fwd: frames exceed the padded clip");
+    return fail(SE_ERR_UNSUPPORTED, "%s: win %d / hop %d / fft %d outside the FFT engine (fft 512, hop <= 256, "
+                                    "ceil(win/hop) <= %d)", nm, win, hop, fft, MAXJ);
+  SE_REQUIRE(pad < L && (T - 1) * hop + win <= L + 2 * (int64_t)pad, "%s: frames exceed the padded clip", nm);
   if (B == 0 || T == 0) return SE_OK;
   int64_t tiles = (T + TILE - 1) / TILE;
-  SE_REQUIRE(T < (1 << 30) && tiles * B < (1ll << 31), "se_stft_fft_fwd: batch x frame count too large");
+  SE_REQUIRE(T < (1 << 30) && tiles * B < (1ll << 31), "%s: batch x frame count too large", nm);
   int xs_cap = ((TILE - 1) * hop + NFFT + 3) & ~3;
   size_t smem = (size_t)(TILE / 2) * ZPITCH * sizeof(float2) + 16 * 32 * sizeof(float2) + NFFT * sizeof(float) +
                 2 * (size_t)xs_cap * sizeof(float);
   static se::PerDevice<bool> attr_set_pd(false);
   bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute(stft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024));
+    SE_CUDA(cudaFuncSetAttribute(stft_fft_kernel<TIn>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024));
     attr_set = true;
   }
   int total = (int)(tiles * B);
   int grid = total < 2 * num_sms() ? total : 2 * num_sms();
-  stft_fft_kernel<<<grid, FTHREADS, smem, (cudaStream_t)stream>>>(x, L, window, win, hop, pad, out, (int)T, (int)tiles,
-                                                                 total, xs_cap);
-  return check_launch("se_stft_fft_fwd");
+  stft_fft_kernel<TIn><<<grid, FTHREADS, smem, (cudaStream_t)stream>>>(x, L, window, win, hop, pad, out, (int)T,
+                                                                      (int)tiles, total, xs_cap);
+  return check_launch(nm);
 }
 
-extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
-                                const float* scale, int64_t crop_front, int64_t out_len, float* out, void* stream) {
-  using namespace se;
-  SE_REQUIRE(spec && window && out, "se_istft_fft_fwd: null pointer");
-  SE_REQUIRE(B >= 0 && T >= 0 && crop_front >= 0 && out_len >= 0, "se_istft_fft_fwd: bad dims");
+template <typename TOut>
+int istft_fft_launch(const char* nm, const float* spec, int64_t B, int64_t T, const float* window, int win, int hop,
+                     int fft, const float* scale, int64_t crop_front, int64_t out_len, TOut* out, void* stream) {
+  SE_REQUIRE(spec && window && out, "%s: null pointer", nm);
+  SE_REQUIRE(B >= 0 && T >= 0 && crop_front >= 0 && out_len >= 0, "%s: bad dims", nm);
   if (!fft_framing_ok(win, hop, fft))
-    return fail(SE_ERR_UNSUPPORTED, "se_istft_fft_fwd: win %d / hop %d / fft %d outside the FFT engine (fft 512, hop <= 256, "
-                                    "ceil(win/hop) <= %d)", win, hop, fft, MAXJ);
+    return fail(SE_ERR_UNSUPPORTED, "%s: win %d / hop %d / fft %d outside the FFT engine (fft 512, hop <= 256, "
+                                    "ceil(win/hop) <= %d)", nm, win, hop, fft, MAXJ);
   if (B == 0 || T == 0 || out_len == 0) return SE_OK;
+  SE_REQUIRE(crop_front + out_len <= (T - 1) * (int64_t)hop + win, "%s: crop window outside the overlap-add length", nm);
   int J = (win + hop - 1) / hop;
-  SE_REQUIRE(T < (1 << 30), "se_istft_fft_fwd: frame count too large");
+  SE_REQUIRE(T < (1 << 30), "%s: frame count too large", nm);
   int Q = (int)T + J - 1;
   int halo = (J - 1 + 1) & ~1;
   int tq = TILE - halo;                                       // hop blocks of output per tile (32 frames with the halo)
   int64_t tiles = (Q + tq - 1) / tq;
-  SE_REQUIRE(tiles * B < (1ll << 31), "se_istft_fft_fwd: batch x frame count too large");
+  SE_REQUIRE(tiles * B < (1ll << 31), "%s: batch x frame count too large", nm);
   size_t smem = (size_t)(fft + 2) * IPITCH * sizeof(float) + (size_t)WARPS * 16 * TPITCH * sizeof(float2);
   static se::PerDevice<bool> attr_set_pd(false);
   bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute(istft_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    SE_CUDA(cudaFuncSetAttribute(istft_fft_kernel<TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set = true;
   }
   // closed form of pinv for the first `win` rows of the real DFT:
@@ -545,8 +575,30 @@ extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const f
   int grid = total < 2 * num_sms() ? total : 2 * num_sms();
   // i / hop for 0 <= i < 32 * 256 as __umulhi(i, magic): exact for these small dividends
   unsigned hop_magic = (unsigned)((0x100000000ull + (unsigned)hop - 1) / (unsigned)hop);
-  istft_fft_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(spec, (int)T, window, win, hop, J, c_even, c_odd, scale,
-                                                                  crop_front, out_len, out, Q, tq, (int)tiles, total,
-                                                                  hop_magic);
-  return check_launch("se_istft_fft_fwd");
+  istft_fft_kernel<TOut><<<grid, THREADS, smem, (cudaStream_t)stream>>>(spec, (int)T, window, win, hop, J, c_even, c_odd,
+                                                                       scale, crop_front, out_len, out, Q, tq, (int)tiles,
+                                                                       total, hop_magic);
+  return check_launch(nm);
+}
+
+}  // namespace
+}  // namespace se
+
+extern "C" int se_stft_fft_fwd(const float* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
+                               int pad, float* out, int64_t T, void* stream) {
+  return se::stft_fft_launch<float>("se_stft_fft_fwd", x, B, L, window, win, hop, fft, pad, out, T, stream);
+}
+extern "C" int se_stft_fft_fwd_pcm16(const int16_t* x, int64_t B, int64_t L, const float* window, int win, int hop, int fft,
+                                     int pad, float* out, int64_t T, void* stream) {
+  return se::stft_fft_launch<int16_t>("se_stft_fft_fwd_pcm16", x, B, L, window, win, hop, fft, pad, out, T, stream);
+}
+extern "C" int se_istft_fft_fwd(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
+                                const float* scale, int64_t crop_front, int64_t out_len, float* out, void* stream) {
+  return se::istft_fft_launch<float>("se_istft_fft_fwd", spec, B, T, window, win, hop, fft, scale, crop_front, out_len, out,
+                                     stream);
+}
+extern "C" int se_istft_fft_fwd_pcm16(const float* spec, int64_t B, int64_t T, const float* window, int win, int hop, int fft,
+                                      const float* scale, int64_t crop_front, int64_t out_len, int16_t* out, void* stream) {
+  return se::istft_fft_launch<int16_t>("se_istft_fft_fwd_pcm16", spec, B, T, window, win, hop, fft, scale, crop_front,
+                                       out_len, out, stream);
 }

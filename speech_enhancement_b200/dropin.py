@@ -138,7 +138,7 @@ def accelerate(model):
     """Put the chained engine behind `model.forward` of a reference DCCRN / DCUNet / FRCRN instance (built after
     `install()`; the class is the reference's own, unmodified).  Returns `model`.
 
-    The chained forward serves CUDA fp32 inputs in eval mode under torch.no_grad().  Everything else (training,
+    The chained forward serves CUDA fp32 (or int16 PCM) inputs in eval mode under torch.no_grad().  Everything else (training,
     autograd, CPU tensors) runs the reference's own forward, i.e. the module-by-module drop-in; the first such
     call per reason emits a RuntimeWarning so the slower path is never taken silently.  A model whose structure
     is not recognised raises here instead of being left half-accelerated."""
@@ -167,10 +167,13 @@ def accelerate(model):
             why = 'the model is in training mode (batch-statistics complex BN is not folded)'
         elif torch.is_grad_enabled():
             why = 'autograd is enabled (call under torch.no_grad() for the chained engine)'
-        elif not (torch.is_tensor(x) and x.is_cuda and x.dtype == torch.float32):
-            why = 'the input is not a CUDA float32 tensor'
+        elif not (torch.is_tensor(x) and x.is_cuda and x.dtype in (torch.float32, torch.int16)):
+            why = 'the input is not a CUDA float32 (or int16 PCM) tensor'
         else:
             return view._forward_fused(x)
+        if getattr(model.istft, 'pcm16_out', False):
+            # the reference's own forward ends in clamp_(wav, -1, 1), which would wreck int16 samples
+            raise RuntimeError(f'{kind}: istft.pcm16_out needs the chained forward, but {why}')
         if why not in warned:
             warned.add(why)
             warnings.warn(f'{kind}: running the reference\'s module-by-module forward because {why}',

@@ -107,3 +107,24 @@ def polar_to_rect(mags, phase):
         _abi.check(_abi.lib().se_polar_to_rect(_abi.ptr(mags), _abi.ptr(phase), B, F, T, _abi.ptr(out),
                                                _abi.stream_ptr()))
     return out
+
+
+def pcm16_to_float(x):
+    """int16 PCM_S 16 samples -> fp32 in [-1, 1) (torchaudio.load's x / 32768; audio_dataset.py:12-21)."""
+    if not (torch.is_tensor(x) and x.is_cuda and x.dtype == torch.int16):
+        raise RuntimeError('pcm16_to_float: expected an int16 CUDA tensor')
+    x = x.contiguous()
+    y = torch.empty(x.shape, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        _abi.check(_abi.lib().se_pcm16_to_f32(_abi.ptr(x), x.numel(), _abi.ptr(y), _abi.stream_ptr()))
+    return y
+
+
+def pcm16_from_float(x):
+    """fp32 waveform -> int16 PCM_S 16 as the reference's savers write it (mix_audio.py:144-146, trainer.py:255-262):
+    clamp(-1, 1), x * 32768 rounded to nearest (ties to even), saturated at 32767."""
+    x = _abi.require_cuda_f32(x, 'pcm16_from_float(x)').contiguous()
+    y = torch.empty(x.shape, device=x.device, dtype=torch.int16)
+    with torch.cuda.device(x.device):
+        _abi.check(_abi.lib().se_pcm16_from_f32(_abi.ptr(x), x.numel(), _abi.ptr(y), _abi.stream_ptr()))
+    return y

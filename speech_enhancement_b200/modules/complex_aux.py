@@ -179,6 +179,100 @@ class ComplexLSTM(_abi.InvalidatesCaches, nn.Module):
         self.imag_lstm.flatten_parameters()
 
 
+def _cbn_closed_form(S, n, eps, W, Bv):
+    """[C, 5] sums -> (Zrr, Zri, Zir, Zii, cr, ci, M, V): the batch statistics and whitening of complex_nn.py:266-322
+    on C-sized fp64 tensors (differentiable: the backward of the fused train-mode kernels runs autograd through it)."""
+    Mr, Mi = S[:, 0] / n, S[:, 1] / n
+    Vrr, Vii, Vri = S[:, 2] / n - Mr * Mr, S[:, 3] / n - Mi * Mi, S[:, 4] / n - Mr * Mi
+    vrr, vii = Vrr + eps, Vii + eps
+    s_ = (vrr * vii - Vri * Vri).sqrt()
+    t_ = (vrr + vii + 2 * s_).sqrt()
+    rst = (s_ * t_).reciprocal()
+    Urr, Uii, Uri = (s_ + vii) * rst, (s_ + vrr) * rst, -Vri * rst
+    if W is None:
+        Zrr, Zri, Zir, Zii = Urr, Uri, Uri, Uii
+    else:
+        Wrr, Wri, Wii = W
+        Zrr, Zri, Zir, Zii = Wrr * Urr + Wri * Uri, Wrr * Uri + Wri * Uii, Wri * Urr + Wii * Uri, Wri * Uri + Wii * Uii
+    cr, ci = -(Zrr * Mr + Zri * Mi), -(Zir * Mr + Zii * Mi)
+    if Bv is not None:
+        cr, ci = cr + Bv[0], ci + Bv[1]
+    return (Zrr, Zri, Zir, Zii, cr, ci), (Mr, Mi), (Vrr, Vri, Vii)
+
+
+class _CBNTrainFn(torch.autograd.Function):
+    """train-mode complex BN as four HBM passes of csrc/cbn_train.cu around C-sized host algebra (one autograd node
+    instead of the ~40 full-tensor ops of complex_nn.py:244-322 and their backward)"""
+
+    @staticmethod
+    def forward(ctx, x, eps, Wrr, Wri, Wii, Br, Bi):
+        B, C2, H, W = x.shape
+        C = C2 // 2
+        lib = _abi.lib()
+        n = B * H * W
+        with torch.cuda.device(x.device), _abi.stage('cbn'):
+            splits = lib.se_cbn_splits(B, C, H, W)
+            partial = torch.empty((C, splits, 5), device=x.device, dtype=torch.float64)
+            _abi.check(lib.se_cbn_stats(_abi.ptr(x), B, C, H, W, _abi.ptr(partial), _abi.stream_ptr()))
+            S = partial.sum(1)
+            Wd = None if Wrr is None else (Wrr.detach().double(), Wri.detach().double(), Wii.detach().double())
+            Bd = None if Br is None else (Br.detach().double(), Bi.detach().double())
+            coef, M, V = _cbn_closed_form(S, n, eps, Wd, Bd)
+            coef_t = torch.stack(coef).float().contiguous()
+            y = torch.empty_like(x)
+            _abi.check(lib.se_cbn_apply(_abi.ptr(x), _abi.ptr(coef_t), B, C, H, W, _abi.ptr(y), _abi.stream_ptr()))
+        ctx.save_for_backward(x, S, Wrr, Wri, Wii, Br, Bi)
+        ctx.eps = eps
+        stats = torch.stack([M[0], M[1], V[0], V[1], V[2]]).float()
+        ctx.mark_non_differentiable(stats)
+        return y, stats
+
+    @staticmethod
+    def backward(ctx, g, _g_stats):
+        x, S, Wrr, Wri, Wii, Br, Bi = ctx.saved_tensors
+        B, C2, H, W = x.shape
+        C = C2 // 2
+        lib = _abi.lib()
+        g = g.contiguous()
+        with torch.cuda.device(x.device), _abi.stage('cbn_bwd'):
+            splits = lib.se_cbn_splits(B, C, H, W)
+            partial = torch.empty((C, splits, 6), device=x.device, dtype=torch.float64)
+            _abi.check(lib.se_cbn_bwd_stats(_abi.ptr(x), _abi.ptr(g), B, C, H, W, _abi.ptr(partial), _abi.stream_ptr()))
+            G = partial.sum(1)
+            with torch.enable_grad():
+                S_ = S.detach().requires_grad_(True)
+                leaves = [S_]
+                Wd = Bd = None
+                if Wrr is not None:
+                    Wd = tuple(t.detach().double().requires_grad_(True) for t in (Wrr, Wri, Wii))
+                    leaves += list(Wd)
+                if Br is not None:
+                    Bd = tuple(t.detach().double().requires_grad_(True) for t in (Br, Bi))
+                    leaves += list(Bd)
+                coef, _, _ = _cbn_closed_form(S_, B * H * W, ctx.eps, Wd, Bd)
+                # dL/dZrr = sum gr xr, dL/dZri = sum gr xi, dL/dZir = sum gi xr, dL/dZii = sum gi xi, dL/dc = sum g
+                grads = torch.autograd.grad(list(coef), leaves, [G[:, 2], G[:, 3], G[:, 4], G[:, 5], G[:, 0], G[:, 1]],
+                                            allow_unused=True)
+            dS = grads[0]
+            k = torch.stack([coef[0].detach(), coef[1].detach(), coef[2].detach(), coef[3].detach(),
+                             dS[:, 0], 2 * dS[:, 2], dS[:, 4], dS[:, 1], dS[:, 4], 2 * dS[:, 3]]).float().contiguous()
+            dx = torch.empty_like(x)
+            _abi.check(lib.se_cbn_bwd_apply(_abi.ptr(x), _abi.ptr(g), _abi.ptr(k), B, C, H, W, _abi.ptr(dx),
+                                            _abi.stream_ptr()))
+        out = [dx, None]
+        i = 1
+        if Wrr is not None:
+            out += [grads[i].to(Wrr.dtype), grads[i + 1].to(Wri.dtype), grads[i + 2].to(Wii.dtype)]
+            i += 3
+        else:
+            out += [None, None, None]
+        if Br is not None:
+            out += [grads[i].to(Br.dtype), grads[i + 1].to(Bi.dtype)]
+        else:
+            out += [None, None]
+        return tuple(out)
+
+
 class ComplexBatchNorm2d(_abi.InvalidatesCaches, nn.Module):
     """2x2 whitening batch norm of Trabelsi et al. (complex_nn.py:148-329)."""
 
@@ -237,10 +331,29 @@ class ComplexBatchNorm2d(_abi.InvalidatesCaches, nn.Module):
         return (Wrr * Urr + Wri * Uri, Wrr * Uri + Wri * Uii,
                 Wri * Urr + Wii * Uri, Wri * Uri + Wii * Uii)
 
+    fused_train = True      # class switch: False keeps the train-mode forward on plain PyTorch ops
+
+    def _forward_train_fused(self, x):
+        """batch statistics + whitening as csrc/cbn_train.cu passes (one autograd node), running stats by lerp_"""
+        f = 0.0
+        if self.training and self.track_running_stats:
+            self.num_batches_tracked += 1
+            f = 1.0 / self.num_batches_tracked.item() if self.momentum is None else self.momentum
+        a = (self.Wrr, self.Wri, self.Wii, self.Br, self.Bi) if self.affine else (None,) * 5
+        y, stats = _CBNTrainFn.apply(x.contiguous(), float(self.eps), *a)
+        if self.track_running_stats:
+            with torch.no_grad():
+                self.RMr.lerp_(stats[0], f); self.RMi.lerp_(stats[1], f)
+                self.RVrr.lerp_(stats[2], f); self.RVri.lerp_(stats[3], f); self.RVii.lerp_(stats[4], f)
+        return y
+
     def forward(self, inputs):
+        training = self.training or not self.track_running_stats
+        if (training and self.fused_train and inputs.is_cuda and inputs.dtype == torch.float32 and inputs.dim() == 4
+                and self.complex_axis == 1 and inputs.shape[0] * inputs.shape[2] * inputs.shape[3] > 0):
+            return self._forward_train_fused(inputs)
         xr, xi = torch.chunk(inputs, 2, dim=self.complex_axis)
         vdim = [1] * xr.dim(); vdim[1] = xr.size(1)
-        training = self.training or not self.track_running_stats
         if training:
             f = 0.0
             if self.training and self.track_running_stats:

@@ -1,0 +1,64 @@
+"""Phase-folded transposed convolution (the sh*sw output phases of a ComplexConvTranspose2d as column groups of one
+stride-1 convolution, chain.FusedBlock.fold) against the per-tap form of the same engine and the fp64 CPU oracle."""
+import pytest
+import torch
+
+import oracle
+import speech_enhancement_b200 as se
+from speech_enhancement_b200 import chain
+from conftest import rand, rel_l2
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+#        cin2, cout2, kernel, stride, padding, output_padding, B, H,  W,  two sources, bias
+CASES = [(128, 32, (5, 2), (2, 1), (2, 0), (1, 0), 2, 64, 70, True, False),     # DCCRN dec4
+         (256, 64, (5, 2), (2, 1), (2, 0), (1, 0), 3, 32, 41, True, False),     # DCCRN dec3
+         (128, 64, (7, 5), (2, 2), (3, 2), (0, 0), 2, 33, 29, True, False),     # DCUNet dec7
+         (64, 24, (5, 3), (2, 2), (2, 1), (0, 0), 2, 9, 17, False, True),       # 24 channels: padded per-phase group
+         (64, 48, (3, 3), (2, 2), (0, 0), (1, 1), 1, 7, 11, False, True),       # no padding: offsets start below zero
+         (32, 90, (5, 3), (2, 1), (2, 1), (0, 0), 2, 6, 13, False, False),      # 90 channels (DCUNet-large pads to 192)
+         (64, 16, (4, 4), (2, 2), (1, 1), (0, 0), 2, 8, 8, False, True),        # even kernel
+         (64, 32, (2, 3), (3, 1), (0, 1), (2, 0), 2, 5, 9, False, False)]       # kernel smaller than the stride
+
+
+@pytest.mark.parametrize('cin2,cout2,k,s,p,op,B,H,W,two,bias', CASES)
+def test_folded_block_matches_per_tap_form_and_oracle(cin2, cout2, k, s, p, op, B, H, W, two, bias, monkeypatch):
+    m = se.ComplexConvTranspose2d(cin2, cout2, k, stride=s, padding=p, output_padding=op, bias=bias)
+    sd = {kk: rand(v.shape, 60 + j, 0.1) for j, (kk, v) in enumerate(sorted(m.state_dict().items()))}
+    m.load_state_dict(sd)
+    m.to(DEV)
+    srcs_c = [cin2 // 2, cin2 // 2] if two else [cin2]
+    xs = [rand((B, c, H, W), 70 + i).to(DEV) for i, c in enumerate(srcs_c)]
+    full = se.complex_concat(xs, dim=1) if two else xs[0]
+    rc, ic = m.real_conv, m.imag_conv
+    want = oracle.cconvT2d_ref(full.cpu().double(), rc.weight.cpu().double(), ic.weight.cpu().double(),
+                               rc.bias.cpu().double() if bias else None, ic.bias.cpu().double() if bias else None,
+                               s, p, op, (1, 1))
+    want = torch.nn.functional.leaky_relu(want, 0.2)
+    outs = {}
+    for mode in ('0', '1'):
+        monkeypatch.setattr(chain, 'FOLD_MODE', mode)
+        blk = chain.FusedBlock(m, None, torch.nn.LeakyReLU(0.2), src_channels=srcs_c, concat='complex')
+        nph_cols = s[0] * s[1] * ((cout2 + 31) // 32 * 32)
+        assert (blk.fold is not None) == (mode == '1' and nph_cols <= 256)
+        with torch.no_grad():
+            act, _ = blk([chain.cl2_from_nchw(x) for x in xs], out_cl2=True)
+            # poison check for the pad channels: consumers may read them (they must be exact zeros)
+            assert (act.data[..., cout2:] == 0).all()
+            outs[mode] = chain.cl2_to_nchw(act).cpu()
+    assert outs['1'].shape == want.shape
+    assert rel_l2(outs['0'], want) < 2e-4
+    assert rel_l2(outs['1'], want) < 2e-4
+    assert rel_l2(outs['1'], outs['0']) < 2e-5
+
+
+def test_auto_mode_folds_the_layers_the_cost_model_names(monkeypatch):
+    monkeypatch.setattr(chain, 'FOLD_MODE', 'auto')
+    mk = lambda cin, cout, k, s, p: se.ComplexConvTranspose2d(cin, cout, k, stride=s, padding=p)
+    assert chain.FusedBlock(mk(128, 32, (5, 2), (2, 1), (2, 0))).fold is not None      # DCCRN dec4
+    assert chain.FusedBlock(mk(256, 64, (5, 2), (2, 1), (2, 0))).fold is not None      # DCCRN dec3
+    assert chain.FusedBlock(mk(512, 128, (5, 2), (2, 1), (2, 0))).fold is None         # N = 256 already
+    assert chain.FusedBlock(mk(256, 64, (7, 5), (2, 2), (3, 2))).fold is None          # DCUNet dec7: 256 columns lose
+    assert chain.FusedBlock(mk(256, 128, (5, 2), (2, 1), (0, 0))).fold is None         # FRCRN decoder
+    assert chain.FusedBlock(mk(128, 64, (1, 7), (1, 1), (0, 3))).fold is None          # stride 1: no phases
