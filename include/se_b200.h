@@ -190,12 +190,15 @@ typedef struct se_cconv_args {
   /* optional real channel count of every source (0 = src_Cp): channels [src_C, src_Cp) are zero in the CL2
    * activations and in the prepared weights, so the engine skips 16-channel k-steps that are all padding. */
   int src_C[2];
-  /* optional phase folding (0 or 1 = off): the launch is a stride-1 forward convolution whose Cout2 = fold_h * fold_w *
-   * fold_cg accumulator columns are the output phases of a ComplexConvTranspose2d with stride (fold_h, fold_w) side by
-   * side -- column group ph = r * fold_w + s of quotient pixel (q, p) is output pixel (q * fold_h + r, p * fold_w + s),
-   * channel = column - ph * fold_cg (< fold_cout2).  Ho, Wo are the real output extent; `wq` / `bias` are built for the
-   * folded columns (zero weight blocks where a phase has no tap at an input offset).  One wide MMA per input offset
-   * replaces one narrow MMA per kernel tap: complex_nn.py:80-91 layers with few output channels.                    */
+  /* optional output folding (0 or 1 = off): the launch is a forward convolution over the QUOTIENT grid whose Cout2 =
+   * fold_h * fold_w * fold_cg accumulator columns are fold_h x fold_w neighbouring output pixels side by side -- column
+   * group ph = r * fold_w + s of quotient pixel (q, p) is output pixel (q * fold_h + r, p * fold_w + s), channel =
+   * column - ph * fold_cg (< fold_cout2).  Ho, Wo are the real output extent; kh, kw, sh, sw, ph, pw describe the
+   * convolution in quotient coordinates; `wq` / `bias` are built for the folded columns (zero weight blocks where a
+   * pixel has no tap at an input offset).  Two uses: the sh * sw output phases of a ComplexConvTranspose2d as ONE stride-1
+   * convolution (one wide MMA per input offset instead of one narrow MMA per kernel tap), and pixel pairs of a narrow
+   * forward / stride-1 layer (k + s taps of 2 N columns instead of 2 k taps of N): complex_nn.py:67-91 layers with few
+   * output channels, where every 128-row MMA is bound by its A-operand read, not by N.                              */
   int fold_h, fold_w, fold_cg, fold_cout2;
 } se_cconv_args;
 SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);

@@ -18,6 +18,8 @@ import sys
 
 M = {'time': 'gpu__time_duration.sum',
      'tensor': 'TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed',
+     'hmma': 'TPC.TriageCompute.sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg',
+     'memtensor': 'sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed',
      'tensor2': 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed',
      'tensor3': 'sm__inst_executed_pipe_tensor.avg.pct_of_peak_sustained_active',
      'sm': 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
@@ -104,6 +106,7 @@ def main():
     ap.add_argument('log')
     ap.add_argument('--traffic-json')
     ap.add_argument('--model', default='dccrn')
+    ap.add_argument('--cublas-ref', help='raw CSV of scripts/ncu_cublas_ref.py under the same ncu settings')
     a = ap.parse_args()
     rows = read_report(a.report)
     head, exp = read_log(a.log)
@@ -114,7 +117,19 @@ def main():
           'cold-cache replays; times are not bench times)')
     if len(rows) != len(exp):
         print(f'# WARNING: launch count mismatch, rows are matched in order as far as they go')
-    print(f'{"layer":28s} {"shape":22s} {"plan":38s} {"time us":>8s} {"tensor%":>7s} {"sm%":>5s} {"dram%":>5s} '
+    ref_rate = None
+    if a.cublas_ref:
+        ref = read_report(a.cublas_ref)
+        rates = [r['hmma'] / r['time'] for r in ref if r.get('hmma') and r.get('time')]
+        ref_rate = sum(rates) / len(rates)
+        pcts = ', '.join(f'{r.get("tensor", float("nan")):.1f}' for r in ref)
+        print(f'# tensor-pipe reference: cuBLAS bf16 8192^3 under the same ncu settings ({a.cublas_ref}): '
+              f'{sum(r["time"] for r in ref) / len(ref):.1f} us per launch = '
+              f'{2 * 8192 ** 3 / (sum(r["time"] for r in ref) / len(ref)) / 1e6:.0f} TFLOP/s, hmma-subpipe active '
+              f'{ref_rate:.0f} cycles/us.  The percent counter sm__pipe_tensor_cycles_active_realtime...pct_of_peak_sustained_elapsed '
+              f'read {pcts} % on these identical launches, i.e. it is not reproducible; "vs cuBLAS" below is '
+              'hmma-active cycles per microsecond of the launch relative to that cuBLAS run (stable to 0.4 %).')
+    print(f'{"layer":28s} {"shape":22s} {"plan":38s} {"time us":>8s} {"tensor%":>7s} {"vs cuBLAS":>9s} {"sm%":>5s} {"dram%":>5s} '
           f'{"DRAM MB":>8s} {"alg MB":>8s} {"ratio":>5s} {"TFLOP/s":>7s} {"regs":>4s}  kernel')
     tot_dram = tot_alg = tot_t = tot_fl = 0.0
     for r, e in zip(rows, exp):
@@ -130,7 +145,8 @@ def main():
             tot_fl += e['flop']
         ratio = f'{dram / e["alg"]:5.2f}' if e['alg'] else '    -'
         tf = f'{e["flop"] / r["time"] / 1e6:7.1f}' if e['flop'] and r.get('time') else '      -'
-        print(f'{e["label"]:28s} {e["shape"]:22s} {str(e["plan"]):38s} {r.get("time", 0):8.1f} {tensor:7.1f} {r.get("sm", 0):5.1f} '
+        vs = f'{r["hmma"] / r["time"] / ref_rate:9.2f}' if ref_rate and r.get('hmma') and r.get('time') else '        -'
+        print(f'{e["label"]:28s} {e["shape"]:22s} {str(e["plan"]):38s} {r.get("time", 0):8.1f} {tensor:7.1f} {vs} {r.get("sm", 0):5.1f} '
               f'{r.get("dram", 0):5.1f} {dram / 1e6:8.1f} {e["alg"] / 1e6:8.1f} {ratio} {tf} {int(r.get("regs", 0)):4d}  '
               f'{r["kernel"][:40]}')
     print(f'# conv launches: DRAM {tot_dram / 1e9:.3f} GB vs algorithmic {tot_alg / 1e9:.3f} GB = {tot_dram / tot_alg:.2f}x; '

@@ -159,6 +159,23 @@ def fold_transposed_weight(p4, sh, sw, fold):
     return wf
 
 
+def fold_pixel_pairs_weight(p4, axis, stride, cg):
+    """forward-convolution operand [Cout2, Cin2, kh, kw] (out[q] = sum_d x[q*s - p + d] w[d]) -> the operand of the
+    convolution that computes TWO adjacent output pixels along `axis` (0 = rows, 1 = columns) per GEMM row:
+    [2 * cg, Cin2, kh', kw'] with the folded axis extended to k + s taps and walked at stride 2 s.  Output 2 q + ph
+    reads input q * 2s - p + (ph * s + d), so column group ph carries w[d] at tap ph * s + d and zeros elsewhere."""
+    cout2, cin2, kh, kw = p4.shape
+    ext = (kh + stride, kw) if axis == 0 else (kh, kw + stride)
+    wf = torch.zeros((2 * cg, cin2) + ext, device=p4.device, dtype=p4.dtype)
+    for ph in range(2):
+        o = ph * stride
+        if axis == 0:
+            wf[ph * cg:ph * cg + cout2, :, o:o + kh, :] = p4
+        else:
+            wf[ph * cg:ph * cg + cout2, :, :, o:o + kw] = p4
+    return wf
+
+
 # SE_CONV_FOLD: 'auto' (fold where the MMA cost model says it pays), '0' never, '1' wherever the shape allows
 FOLD_MODE = os.environ.get('SE_CONV_FOLD', 'auto')
 
@@ -207,7 +224,22 @@ class FusedBlock:
                 gain = (self.kh * self.kw * _mma_cost((self.cout2 + 15) // 16 * 16)
                         / (len(es) * len(fs) * _mma_cost(nph * cg)))
                 if FOLD_MODE == '1' or (gain > 1.1 and nph * cg <= 128):
-                    self.fold = dict(oh=oh, ow=ow, es=es, fs=fs, cg=cg, nph=nph, gain=gain)
+                    self.fold = dict(kind='phase', oh=oh, ow=ow, es=es, fs=fs, cg=cg, nph=nph, gain=gain)
+        # narrow layers WITHOUT output phases (forward convolutions, stride-1 transposed ones): two adjacent output
+        # pixels along one axis share a GEMM row -- that axis is walked at twice the stride with k + s taps, the two
+        # pixels are two column groups (N = 2 x channels).  k taps of N columns per pixel become (k + s) / 2 of 2 N.
+        if (self.fold is None and not self.scatter_form and FOLD_MODE != '0'
+                and (not self.transposed or (self.sh, self.sw) == (1, 1))):
+            cg = (self.cout2 + 31) // 32 * 32
+            npad = (self.cout2 + 15) // 16 * 16
+            best = None
+            for axis, (k, st) in enumerate(((self.kh, self.sh), (self.kw, self.sw))):
+                gain = 2 * k * _mma_cost(npad) / ((k + st) * _mma_cost(2 * cg))
+                if best is None or gain > best[1]:
+                    best = (axis, gain)
+            if 2 * cg <= 256 and (self.kh + self.sh) * (self.kw + self.sw) <= 49 and \
+                    (FOLD_MODE == '1' or (best[1] > 1.1 and 2 * cg <= 128)):
+                self.fold = dict(kind='pixel', axis=best[0], cg=cg, nph=2, gain=best[1])
         self._key = None
         self._ops = None
 
@@ -264,13 +296,19 @@ class FusedBlock:
             wq_fold = bias_fold = None
             if self.fold is not None:
                 f = self.fold
-                es, fs, cg, nph = f['es'], f['fs'], f['cg'], f['nph']
-                wf = fold_transposed_weight(packed.view(2 * co, 2 * ci, kh, kw), self.sh, self.sw, f)
-                wf = wf.reshape(nph * cg, 2 * ci * len(es) * len(fs)).contiguous()
+                cg, nph = f['cg'], f['nph']
+                p4 = packed.view(2 * co, 2 * ci, kh, kw)
+                if f['kind'] == 'phase':
+                    wf = fold_transposed_weight(p4, self.sh, self.sw, f)
+                else:
+                    if self.transposed:       # stride-1 transposed convolution = forward convolution with flipped taps
+                        p4 = p4.flip(2, 3)
+                    wf = fold_pixel_pairs_weight(p4, f['axis'], self.sh if f['axis'] == 0 else self.sw, cg)
+                ntap = wf.shape[2] * wf.shape[3]
+                wf = wf.reshape(nph * cg, 2 * ci * ntap).contiguous()
                 bias_fold = torch.zeros((nph, cg), device=dev, dtype=torch.float32)
                 bias_fold[:, :2 * co] = bias
                 bias_fold = bias_fold.reshape(-1).contiguous()
-                ntap = len(es) * len(fs)
                 wq_fold = torch.empty((lib.se_cconv_wq_elems(nph * cg, cpt, ntap),), device=dev, dtype=torch.bfloat16)
                 with torch.cuda.device(dev):
                     _abi.check(lib.se_cconv_prep_weight(_abi.ptr(wf), nph * cg, 2 * ci, ntap, _abi.ptr(cmap_t), cpt,
@@ -349,12 +387,25 @@ class FusedBlock:
                                                 _abi.ptr(y), _abi.stream_ptr()))
             return None, y
         if self.fold is not None and y is None and y_act is not None:
-            # phase-folded form: stride-1 forward convolution over the input grid, phases as column groups
             f = self.fold
-            a.transposed, a.kh, a.kw, a.sh, a.sw = 0, len(f['es']), len(f['fs']), 1, 1
-            a.ph, a.pw = -f['es'][0], -f['fs'][0]
+            if f['kind'] == 'phase':
+                # phase-folded form: stride-1 forward convolution over the input grid, phases as column groups
+                a.transposed, a.kh, a.kw, a.sh, a.sw = 0, len(f['es']), len(f['fs']), 1, 1
+                a.ph, a.pw = -f['es'][0], -f['fs'][0]
+                a.fold_h, a.fold_w = self.sh, self.sw
+            else:
+                # pixel-pair form: the folded axis is walked at twice the stride with k + s taps
+                kh, kw, sh, sw, ph, pw = self.kh, self.kw, self.sh, self.sw, self.ph, self.pw
+                if self.transposed:           # forward equivalent of a stride-1 transposed convolution
+                    ph, pw = kh - 1 - ph, kw - 1 - pw
+                a.transposed = 0
+                if f['axis'] == 0:
+                    a.kh, a.kw, a.sh, a.sw, a.fold_h, a.fold_w = kh + sh, kw, 2 * sh, sw, 2, 1
+                else:
+                    a.kh, a.kw, a.sh, a.sw, a.fold_h, a.fold_w = kh, kw + sw, sh, 2 * sw, 1, 2
+                a.ph, a.pw = ph, pw
             a.Cout2 = f['nph'] * f['cg']
-            a.fold_h, a.fold_w, a.fold_cg, a.fold_cout2 = self.sh, self.sw, f['cg'], self.cout2
+            a.fold_cg, a.fold_cout2 = f['cg'], self.cout2
             a.wq, a.bias = ops['wq_fold'].data_ptr(), ops['bias_fold'].data_ptr()
         with torch.cuda.device(dev), _abi.stage('cconv'):
             _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))

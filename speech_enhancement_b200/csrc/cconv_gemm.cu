@@ -784,10 +784,10 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     return fail(SE_ERR_UNSUPPORTED, "%s: pad_top/pad_left only for the forward convolution", nm);
   if (a->fold_h > 1 || a->fold_w > 1) {
     const int nph = (a->fold_h > 1 ? a->fold_h : 1) * (a->fold_w > 1 ? a->fold_w : 1);
-    if (a->transposed || a->sh != 1 || a->sw != 1 || a->fold_cg <= 0 || a->fold_cg % 32 != 0 ||
+    if (a->transposed || a->fold_cg <= 0 || a->fold_cg % 32 != 0 ||
         a->Cout2 != nph * a->fold_cg || a->fold_cout2 <= 0 || a->fold_cout2 > a->fold_cg)
-      return fail(SE_ERR_BAD_ARG, "%s: a folded launch is a stride-1 forward convolution with Cout2 = phases * fold_cg "
-                                  "columns, fold_cg a multiple of 32 and fold_cout2 <= fold_cg", nm);
+      return fail(SE_ERR_BAD_ARG, "%s: a folded launch is a forward convolution over the quotient grid with Cout2 = phases "
+                                  "* fold_cg columns, fold_cg a multiple of 32 and fold_cout2 <= fold_cg", nm);
   }
   for (int i = 0; i < a->nsrc; ++i)
     if (a->src_Cp[i] <= 0 || a->src_Cp[i] % 64 != 0)

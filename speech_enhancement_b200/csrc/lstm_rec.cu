@@ -139,7 +139,8 @@ lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0,
   float* __restrict__ h_out = blockIdx.y ? h_out1 : h_out0;
   pre += blockIdx.y * 4 * H;
   extern __shared__ __align__(16) float smem[];
-  float2* w_s = reinterpret_cast<float2*>(smem);     // [KS][NT] (column ca, column cb of thread j)
+  // weights that do not fit the register file: [KS/2][NT] float4 = (wa[k], wa[k+1], wb[k], wb[k+1]) of thread j
+  float4* w_s = reinterpret_cast<float4*>(smem);
   float* h_s = smem + 2 * KS * NT;                   // [2][R][H]
   const int j = threadIdx.x, lane = j & 31;
   const bool upper = lane >= 16;
@@ -148,14 +149,19 @@ lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0,
   const int cb = ca + 2 * H;                         // g | o
   const float bs = upper ? 0.5f : 1.f, bo = upper ? 0.5f : 0.f;   // act(b) = bo + bs * tanh(bs * b)
 
-  float wa[KR], wb[KR];
+  // Packed FP32: a 3-register FFMA issues at half rate on sm_100 (scripts/ffma2_rate.cu: 73 FMA lanes / clk / SM against
+  // 113 for FFMA2), and this loop is nothing but such FMAs.  The two accumulator chains of a column (even k, odd k) are
+  // the two halves of ONE fma.rn.f32x2: weights (w[k], w[k+1]) and h (h[k], h[k+1]) are natural register pairs, the
+  // per-lane arithmetic and its order are those of the scalar loop (bit-identical results), the FMA instruction count halves.
+  float2 wa[KR / 2], wb[KR / 2];
 #pragma unroll
-  for (int k = 0; k < KR; ++k) {
-    wa[k] = __ldg(w_hh + (int64_t)ca * H + k);
-    wb[k] = __ldg(w_hh + (int64_t)cb * H + k);
+  for (int k = 0; k < KR; k += 2) {
+    wa[k / 2] = make_float2(__ldg(w_hh + (int64_t)ca * H + k), __ldg(w_hh + (int64_t)ca * H + k + 1));
+    wb[k / 2] = make_float2(__ldg(w_hh + (int64_t)cb * H + k), __ldg(w_hh + (int64_t)cb * H + k + 1));
   }
-  for (int k = 0; k < KS; ++k)
-    w_s[k * NT + j] = make_float2(__ldg(w_hh + (int64_t)ca * H + KR + k), __ldg(w_hh + (int64_t)cb * H + KR + k));
+  for (int k = 0; k < KS; k += 2)
+    w_s[(k / 2) * NT + j] = make_float4(__ldg(w_hh + (int64_t)ca * H + KR + k), __ldg(w_hh + (int64_t)ca * H + KR + k + 1),
+                                        __ldg(w_hh + (int64_t)cb * H + KR + k), __ldg(w_hh + (int64_t)cb * H + KR + k + 1));
 
   for (int64_t row0 = (int64_t)blockIdx.x * R; row0 < N; row0 += (int64_t)gridDim.x * R) {
     float c[RP];
@@ -177,11 +183,11 @@ lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0,
     for (int64_t t = 0; t < T; ++t) {
       const float* hc = h_s + cur * (R * H);
       float* hn = h_s + (cur ^ 1) * (R * H);
-      float aa[R][2], ab[R][2];
+      float2 aa[R], ab[R];                                       // (even-k chain, odd-k chain)
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        aa[r][0] = nxa[r]; aa[r][1] = 0.f;
-        ab[r][0] = nxb[r]; ab[r][1] = 0.f;
+        aa[r] = make_float2(nxa[r], 0.f);
+        ab[r] = make_float2(nxb[r], 0.f);
         if (t + 1 < T) {
           nxa[r] = __ldg(prow[r] + (t + 1) * pre_ld + ca);
           nxb[r] = __ldg(prow[r] + (t + 1) * pre_ld + cb);
@@ -192,38 +198,31 @@ lstm_rec2_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh0,
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const float4 hv = *reinterpret_cast<const float4*>(hc + r * H + k);
-          aa[r][0] = fmaf(wa[k], hv.x, aa[r][0]);
-          aa[r][1] = fmaf(wa[k + 1], hv.y, aa[r][1]);
-          aa[r][0] = fmaf(wa[k + 2], hv.z, aa[r][0]);
-          aa[r][1] = fmaf(wa[k + 3], hv.w, aa[r][1]);
-          ab[r][0] = fmaf(wb[k], hv.x, ab[r][0]);
-          ab[r][1] = fmaf(wb[k + 1], hv.y, ab[r][1]);
-          ab[r][0] = fmaf(wb[k + 2], hv.z, ab[r][0]);
-          ab[r][1] = fmaf(wb[k + 3], hv.w, ab[r][1]);
+          const float2 h01 = make_float2(hv.x, hv.y), h23 = make_float2(hv.z, hv.w);
+          aa[r] = __ffma2_rn(wa[k / 2], h01, aa[r]);
+          aa[r] = __ffma2_rn(wa[k / 2 + 1], h23, aa[r]);
+          ab[r] = __ffma2_rn(wb[k / 2], h01, ab[r]);
+          ab[r] = __ffma2_rn(wb[k / 2 + 1], h23, ab[r]);
         }
       }
 #pragma unroll 2
       for (int k = 0; k < KS; k += 4) {
-        const float2 w0 = w_s[(k + 0) * NT + j], w1 = w_s[(k + 1) * NT + j];
-        const float2 w2 = w_s[(k + 2) * NT + j], w3 = w_s[(k + 3) * NT + j];
+        const float4 w01 = w_s[(k / 2) * NT + j], w23 = w_s[(k / 2 + 1) * NT + j];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const float4 hv = *reinterpret_cast<const float4*>(hc + r * H + KR + k);
-          aa[r][0] = fmaf(w0.x, hv.x, aa[r][0]);
-          aa[r][1] = fmaf(w1.x, hv.y, aa[r][1]);
-          aa[r][0] = fmaf(w2.x, hv.z, aa[r][0]);
-          aa[r][1] = fmaf(w3.x, hv.w, aa[r][1]);
-          ab[r][0] = fmaf(w0.y, hv.x, ab[r][0]);
-          ab[r][1] = fmaf(w1.y, hv.y, ab[r][1]);
-          ab[r][0] = fmaf(w2.y, hv.z, ab[r][0]);
-          ab[r][1] = fmaf(w3.y, hv.w, ab[r][1]);
+          const float2 h01 = make_float2(hv.x, hv.y), h23 = make_float2(hv.z, hv.w);
+          aa[r] = __ffma2_rn(make_float2(w01.x, w01.y), h01, aa[r]);
+          aa[r] = __ffma2_rn(make_float2(w23.x, w23.y), h23, aa[r]);
+          ab[r] = __ffma2_rn(make_float2(w01.z, w01.w), h01, ab[r]);
+          ab[r] = __ffma2_rn(make_float2(w23.z, w23.w), h23, ab[r]);
         }
       }
       float ga[R], gb[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        ga[r] = 0.5f + 0.5f * tanhf_(0.5f * (aa[r][0] + aa[r][1]));          // i | f
-        gb[r] = bo + bs * tanhf_(bs * (ab[r][0] + ab[r][1]));               // g | o
+        ga[r] = 0.5f + 0.5f * tanhf_(0.5f * (aa[r].x + aa[r].y));            // i | f
+        gb[r] = bo + bs * tanhf_(bs * (ab[r].x + ab[r].y));                 // g | o
       }
 #pragma unroll
       for (int q = 0; q < RP; ++q) {

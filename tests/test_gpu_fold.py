@@ -53,6 +53,51 @@ def test_folded_block_matches_per_tap_form_and_oracle(cin2, cout2, k, s, p, op, 
     assert rel_l2(outs['1'], outs['0']) < 2e-5
 
 
+#            kind  cin2 cout2 kernel  stride  padding  B  H   W   two    bias   pad_left
+PIXEL_CASES = [('C', 64, 64, (7, 1), (1, 1), (3, 0), 2, 37, 29, False, False, 0),     # DCUNet enc0: pairs along H
+               ('C', 64, 64, (1, 7), (1, 1), (0, 3), 2, 19, 41, False, True, 0),      # DCUNet enc1: pairs along W
+               ('T', 128, 64, (1, 7), (1, 1), (0, 3), 2, 21, 33, True, False, 0),     # DCUNet dec8: stride-1 transposed
+               ('C', 32, 64, (5, 2), (2, 1), (2, 0), 3, 40, 27, False, False, 1),     # DCCRN enc1: stride 2 + causal pad
+               ('C', 64, 24, (3, 3), (1, 1), (1, 1), 2, 9, 10, False, True, 0),       # padded column groups, even / odd extents
+               ('T', 64, 32, (3, 5), (1, 1), (1, 2), 1, 8, 7, False, True, 0)]
+
+
+@pytest.mark.parametrize('kind,cin2,cout2,k,s,p,B,H,W,two,bias,pad_left', PIXEL_CASES)
+def test_pixel_pair_folded_block_matches_per_tap_form_and_oracle(kind, cin2, cout2, k, s, p, B, H, W, two, bias, pad_left,
+                                                                 monkeypatch):
+    tr = kind == 'T'
+    mk = se.ComplexConvTranspose2d if tr else se.ComplexConv2d
+    m = mk(cin2, cout2, k, stride=s, padding=p, bias=bias)
+    sd = {kk: rand(v.shape, 80 + j, 0.1) for j, (kk, v) in enumerate(sorted(m.state_dict().items()))}
+    m.load_state_dict(sd)
+    m.to(DEV)
+    srcs_c = [cin2 // 2, cin2 // 2] if two else [cin2]
+    xs = [rand((B, c, H, W), 90 + i).to(DEV) for i, c in enumerate(srcs_c)]
+    full = (se.complex_concat(xs, dim=1) if two else xs[0]).cpu().double()
+    if pad_left:
+        full = torch.nn.functional.pad(full, (pad_left, 0, 0, 0))
+    rc, ic = m.real_conv, m.imag_conv
+    br, bi = (rc.bias.cpu().double(), ic.bias.cpu().double()) if bias else (None, None)
+    if tr:
+        want = oracle.cconvT2d_ref(full, rc.weight.cpu().double(), ic.weight.cpu().double(), br, bi, s, p, (0, 0), (1, 1))
+    else:
+        want = oracle.cconv2d_ref(full, rc.weight.cpu().double(), ic.weight.cpu().double(), br, bi, s, p, (1, 1))
+    want = torch.nn.functional.leaky_relu(want, 0.01)
+    outs = {}
+    for mode in ('0', '1'):
+        monkeypatch.setattr(chain, 'FOLD_MODE', mode)
+        blk = chain.FusedBlock(m, None, torch.nn.LeakyReLU(0.01), src_channels=srcs_c, concat='complex')
+        assert (blk.fold is not None) == (mode == '1') and (blk.fold is None or blk.fold['kind'] == 'pixel')
+        with torch.no_grad():
+            act, _ = blk([chain.cl2_from_nchw(x) for x in xs], pad_left=pad_left, out_cl2=True)
+            assert (act.data[..., cout2:] == 0).all()
+            outs[mode] = chain.cl2_to_nchw(act).cpu()
+    assert outs['1'].shape == want.shape
+    assert rel_l2(outs['0'], want) < 2e-4
+    assert rel_l2(outs['1'], want) < 2e-4
+    assert rel_l2(outs['1'], outs['0']) < 2e-5
+
+
 def test_auto_mode_folds_the_layers_the_cost_model_names(monkeypatch):
     monkeypatch.setattr(chain, 'FOLD_MODE', 'auto')
     mk = lambda cin, cout, k, s, p: se.ComplexConvTranspose2d(cin, cout, k, stride=s, padding=p)
@@ -61,4 +106,9 @@ def test_auto_mode_folds_the_layers_the_cost_model_names(monkeypatch):
     assert chain.FusedBlock(mk(512, 128, (5, 2), (2, 1), (2, 0))).fold is None         # N = 256 already
     assert chain.FusedBlock(mk(256, 64, (7, 5), (2, 2), (3, 2))).fold is None          # DCUNet dec7: 256 columns lose
     assert chain.FusedBlock(mk(256, 128, (5, 2), (2, 1), (0, 0))).fold is None         # FRCRN decoder
-    assert chain.FusedBlock(mk(128, 64, (1, 7), (1, 1), (0, 3))).fold is None          # stride 1: no phases
+    f = chain.FusedBlock(mk(128, 64, (1, 7), (1, 1), (0, 3))).fold                      # DCUNet dec8: stride 1, no phases
+    assert f is not None and f['kind'] == 'pixel' and f['axis'] == 1
+    f = chain.FusedBlock(se.ComplexConv2d(64, 64, (7, 1), padding=(3, 0))).fold         # DCUNet enc0
+    assert f is not None and f['kind'] == 'pixel' and f['axis'] == 0
+    assert chain.FusedBlock(se.ComplexConv2d(128, 256, (5, 2), stride=(2, 1), padding=(2, 0))).fold is None
+    assert chain.FusedBlock(mk(128, 32, (5, 2), (2, 1), (2, 0))).fold['kind'] == 'phase' 
