@@ -228,6 +228,10 @@ class FusedBlock:
         # narrow layers WITHOUT output phases (forward convolutions, stride-1 transposed ones): two adjacent output
         # pixels along one axis share a GEMM row -- that axis is walked at twice the stride with k + s taps, the two
         # pixels are two column groups (N = 2 x channels).  k taps of N columns per pixel become (k + s) / 2 of 2 N.
+        # MEASURED (profiles/r2_pixel_fold_layers.txt, 64 x 4 s): no gain -- DCUNet 7x1 1.61 -> 1.64 ms, 1x7 1.96 -> 1.94,
+        # transposed 1x7 3.61 -> 3.43, DCCRN enc1 (stride 2, element stride 4 in the TMA box) 0.47 -> 0.62 ms: these
+        # short-K layers are bound by per-tile fill + epilogue, not by the MMA count the model looks at.  So this form
+        # is built only on request (SE_CONV_FOLD=1; tests/test_gpu_fold.py keeps it correct), never in 'auto'.
         if (self.fold is None and not self.scatter_form and FOLD_MODE != '0'
                 and (not self.transposed or (self.sh, self.sw) == (1, 1))):
             cg = (self.cout2 + 31) // 32 * 32
@@ -238,7 +242,7 @@ class FusedBlock:
                 if best is None or gain > best[1]:
                     best = (axis, gain)
             if 2 * cg <= 256 and (self.kh + self.sh) * (self.kw + self.sw) <= 49 and \
-                    (FOLD_MODE == '1' or (best[1] > 1.1 and 2 * cg <= 128)):
+                    FOLD_MODE == '1':
                 self.fold = dict(kind='pixel', axis=best[0], cg=cg, nph=2, gain=best[1])
         self._key = None
         self._ops = None

@@ -106,9 +106,12 @@ def test_auto_mode_folds_the_layers_the_cost_model_names(monkeypatch):
     assert chain.FusedBlock(mk(512, 128, (5, 2), (2, 1), (2, 0))).fold is None         # N = 256 already
     assert chain.FusedBlock(mk(256, 64, (7, 5), (2, 2), (3, 2))).fold is None          # DCUNet dec7: 256 columns lose
     assert chain.FusedBlock(mk(256, 128, (5, 2), (2, 1), (0, 0))).fold is None         # FRCRN decoder
-    f = chain.FusedBlock(mk(128, 64, (1, 7), (1, 1), (0, 3))).fold                      # DCUNet dec8: stride 1, no phases
-    assert f is not None and f['kind'] == 'pixel' and f['axis'] == 1
-    f = chain.FusedBlock(se.ComplexConv2d(64, 64, (7, 1), padding=(3, 0))).fold         # DCUNet enc0
+    # pixel-pair folding measured no gain on the short-K layers it applies to: built only under SE_CONV_FOLD=1
+    assert chain.FusedBlock(mk(128, 64, (1, 7), (1, 1), (0, 3))).fold is None           # DCUNet dec8: stride 1, no phases
+    assert chain.FusedBlock(se.ComplexConv2d(64, 64, (7, 1), padding=(3, 0))).fold is None
+    monkeypatch.setattr(chain, 'FOLD_MODE', '1')
+    f = chain.FusedBlock(se.ComplexConv2d(64, 64, (7, 1), padding=(3, 0))).fold
     assert f is not None and f['kind'] == 'pixel' and f['axis'] == 0
+    monkeypatch.setattr(chain, 'FOLD_MODE', 'auto')
     assert chain.FusedBlock(se.ComplexConv2d(128, 256, (5, 2), stride=(2, 1), padding=(2, 0))).fold is None
     assert chain.FusedBlock(mk(128, 32, (5, 2), (2, 1), (2, 0))).fold['kind'] == 'phase' 
