@@ -452,16 +452,15 @@ static int lstm_rec_any(const float* pre, int64_t pre_ld, const float* w0, const
   if (H == 128) {
     static const char* single = getenv("SE_LSTM_SINGLE");      // tuning aid: keep the single-CTA kernel
     if (single && atoi(single) != 0) return dispatch_rows<128, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
-    // cluster kernel: 2 SMs per R rows; pick R so that the row jobs fit one wave of (#SMs / 2) clusters
-    // The cluster kernel (2 SMs per row, weights in registers) has the shorter step and wins while every row
-    // job gets its own cluster; at larger batches the step is issue-bound per row and the single-CTA kernel,
-    // which amortises its shared-memory weight reads over R rows, is ahead (measured: 64 x 4 s, 256 row jobs).
-    const int64_t slots = se::num_sms() / 2, jobs = N * nl;
+    // The 2-CTA cluster kernel (all of W_hh in registers, h halves exchanged through DSMEM) was the small-batch path
+    // while the single-CTA kernel issued scalar FFMAs; with the packed-FFMA2 time loop the single-CTA kernel has the
+    // shorter step at every batch (DCCRN batch 1 / 8 / 16, 4 s: LSTM block 1.49 -> 1.12 ms, the cluster barrier +
+    // DSMEM exchange cost ~0.9 us per step), so the cluster kernel now only runs on request (SE_LSTM_CLUSTER=R).
     static const char* force = getenv("SE_LSTM_CLUSTER");      // tuning aid: R of the cluster kernel to force
     const int fr = force ? atoi(force) : 0;
     if (fr == 4) return se::launch_lstm_cluster<4>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
     if (fr == 2) return se::launch_lstm_cluster<2>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
-    if (fr == 1 || jobs <= slots) return se::launch_lstm_cluster<1>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
+    if (fr == 1) return se::launch_lstm_cluster<1>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
     return dispatch_rows<128, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
   }
   if (H == 64) return dispatch_rows<64, 64>(pre, pre_ld, w0, w1, h0, h1, nl, N, T, s);
