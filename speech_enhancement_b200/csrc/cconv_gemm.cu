@@ -35,7 +35,7 @@ constexpr int kMaxGroups = 48;
 constexpr int kMaxClasses = 4;
 constexpr int kSmemBudget = 226 * 1024;      // dynamic smem we allow ourselves incl. alignment slack (227 KB limit)
 
-struct GTap { uint16_t arow, wslab; };
+struct GTap { uint16_t arow, wslab, acol, pad_; };   // acol: column shift inside a shared halo box (wshare)
 struct GGroup { int16_t row_add, col_add; uint8_t src, ntaps, tap0, pad_; };
 struct GClass {
   int Hq_out, Wq_out, oh_mul, oh_add, ow_mul, ow_add;
@@ -50,6 +50,7 @@ struct GemmParams {
   int kblocks[2], kcol0[2];
   int klast[2];               // descriptor units (16 B = 8 bf16) of real channels in the LAST k-block of a source: 2, 4, 6 or 8
   int TH, TW, nacc;
+  int TWb;                    // pixels per row of the staged A box: TW, or TW + column span rounded up to 8 (wshare)
   int concat, acc_cols;       // concat: a_hi x [b_hi|b_lo] in one MMA (npad <= 128), 2*npad TMEM columns per accumulator
   int nsplit, unit_rows;      // split mode: every hi / lo slab travels as nsplit column slices of unit_rows rows
   int a_half, a_slot, b_unit, SA, SB;
@@ -286,8 +287,8 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
       // counters; the descriptor high word is the constant kDescHi.
       const uint32_t idesc1 = ptx::make_idesc_bf16_f32(128, kConcat ? p.npad : p.unit_rows);
       const uint32_t idesc2 = ptx::make_idesc_bf16_f32(128, 2 * p.npad);     // concat mode only
-      const uint32_t sub16 = (uint32_t)(p.TH * p.TW * 128) >> 4;   // one 128-pixel sub-tile of the halo box
-      const uint32_t tw16 = (uint32_t)(p.TW * 128) >> 4;
+      const uint32_t sub16 = (uint32_t)(p.TH * p.TWb * 128) >> 4;  // one 128-pixel sub-tile of the halo box
+      const uint32_t tw16 = (uint32_t)(p.TWb * 128) >> 4;
       const uint32_t half16 = (uint32_t)p.a_half >> 4;
       const uint32_t a_ring32 = (ptx::smem_u32(a_ring) >> 4) | 0x10000u, a_slot16 = (uint32_t)p.a_slot >> 4;
       const uint32_t b_ring32 = (ptx::smem_u32(b_ring) >> 4) | 0x10000u, b_unit16 = (uint32_t)p.b_unit >> 4;
@@ -316,7 +317,14 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
             ptx::tc_fence_after();
             const uint32_t a_base32 = a_ring32 + sa * a_slot16;
             for (int ti = 0; ti < G.ntaps; ++ti) {
-              const uint32_t a_tap32 = a_base32 + (uint32_t)p.taps[G.tap0 + ti].arow * tw16;
+              const GTap tp = p.taps[G.tap0 + ti];
+              // row-shifted (multiples of 1024 B) and, for single-row kernels, column-shifted (128 B per pixel) view
+              // of the group's halo box.  A column shift moves the start address INSIDE a 1024-byte swizzle atom; the
+              // tensor core applies the 128-byte swizzle to absolute shared-memory address bits (as the TMA did when it
+              // wrote the box), so the shifted start needs nothing else -- measured: with the descriptor's matrix
+              // base-offset field set to (shift & 7) every result is wrong, with 0 every result is right
+              // (tests/test_gpu_fold.py::test_single_row_kernels_share_one_halo_box).
+              const uint32_t a_tap32 = a_base32 + (uint32_t)tp.arow * tw16 + (uint32_t)tp.acol * 8u;
               if (kConcat) {
                 timed_wait(&b_full[sb], pb, prof, w_b);
                 ptx::tc_fence_after();
@@ -600,7 +608,8 @@ static inline int pymod(int a, int b) { int r = a % b; return r < 0 ? r + b : r;
 static inline int floordiv(int a, int b) { return (a - pymod(a, b)) / b; }
 
 // classes / groups / taps of a layer (tile-shape independent part of GemmParams)
-static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max) {
+static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max, bool wshare, int& span_w) {
+  span_w = 0;
   const bool tr = a->transposed != 0;
   const int ph = a->ph + (tr ? 0 : a->pad_top), pw = a->pw + (tr ? 0 : a->pad_left);
   p.ncls = 0;
@@ -657,10 +666,32 @@ static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max)
           G.row_add = (int16_t)(tr ? omin : a->sh * omin + r);
           G.col_add = (int16_t)col_add;
           G.src = 0; G.ntaps = (uint8_t)n; G.tap0 = (uint8_t)nt; G.pad_ = 0;
-          for (int i = 0; i < n; ++i) { p.taps[nt].arow = (uint16_t)(offs[i] - omin); p.taps[nt].wslab = (uint16_t)slabs[i]; ++nt; }
+          for (int i = 0; i < n; ++i) {
+            p.taps[nt].arow = (uint16_t)(offs[i] - omin); p.taps[nt].wslab = (uint16_t)slabs[i];
+            p.taps[nt].acol = 0; p.taps[nt].pad_ = 0; ++nt;
+          }
           if (omax - omin > span_max) span_max = omax - omin;
           p.groups[ng++] = G;
         }
+      }
+      if (wshare && ng - first_group > 1) {
+        // single-row kernel: the kernel columns differ only by a column shift of the SAME input rows, so they share
+        // ONE staged halo box [rows][TW + span][64] and reach it through column-shifted descriptors (128 B per pixel,
+        // matrix base offset = shift & 7) instead of one A load per column: kw x less L2 -> shared-memory fill
+        int cmin = p.groups[first_group].col_add, cmax = cmin;
+        bool ok = true;
+        for (int g = first_group; g < ng; ++g) {
+          ok = ok && p.groups[g].ntaps == 1 && p.groups[g].row_add == p.groups[first_group].row_add;
+          if (p.groups[g].col_add < cmin) cmin = p.groups[g].col_add;
+          if (p.groups[g].col_add > cmax) cmax = p.groups[g].col_add;
+        }
+        if (!ok) return fail(SE_ERR_UNSUPPORTED, "se_cconv_gemm: column sharing needs a single-row kernel");
+        for (int g = first_group; g < ng; ++g)
+          p.taps[p.groups[g].tap0].acol = (uint16_t)(p.groups[g].col_add - cmin);
+        p.groups[first_group].col_add = (int16_t)cmin;
+        p.groups[first_group].ntaps = (uint8_t)(ng - first_group);
+        ng = first_group + 1;
+        if (cmax - cmin > span_w) span_w = cmax - cmin;
       }
       // source 1 re-uses the same taps
       if (a->nsrc == 2) {
@@ -696,7 +727,7 @@ static inline double mma_cycles(int n) {
 constexpr double kFillBytesPerCycle = 36.0;      // sustained L2 -> SMEM fill per SM
 constexpr double kFillLatency = 2500.0;          // request -> data landed (cycles), covers one B unit
 
-static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int span_max, int npad) {
+static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int span_max, int npad, int span_w) {
   TileChoice best{0, 0, 0, 0, 0, 0, 1, 1e300};
   const int nsm = num_sms();
   static const char* ovh_env = getenv("SE_GEMM_TILE_OVH");   // tuning aid: fixed cycles per tile in the cost model
@@ -725,12 +756,14 @@ static TileChoice choose_tile(const se_cconv_args* a, const GemmParams& p, int s
     const int units = concat ? 1 : 2 * nsplit;
     for (int TW = 128; TW >= 8; TW >>= 1) {
       const int TH = 128 / TW;
+      if (span_w > 0 && TW != 128) continue;               // shared column halo: the 128 GEMM rows are ONE image row
+      const int TWb = span_w > 0 ? round_up(TW + span_w, 8) : TW;
       for (int nacc = 1; nacc <= 4; nacc <<= 1) {
         const int tm_need = (nacc - 1) * acc_cols + (concat ? npad : 0) + round_up(npad, 32);
         if (tm_need > 512) continue;
         const int rows = nacc * TH + span_max;
-        if (rows * p.row_mul > 256 || TW * p.col_mul > 256) continue;
-        const int64_t a_slot = 2LL * rows * TW * 128;
+        if (rows * p.row_mul > 256 || TWb * p.col_mul > 256) continue;
+        const int64_t a_slot = 2LL * rows * TWb * 128;
         const int SA = 2;
         int64_t left = kSmemBudget - 1024 - SA * a_slot;
         if (left < 2 * b_unit) continue;
@@ -794,17 +827,21 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
       return fail(SE_ERR_BAD_ARG, "%s: source channel pitch must be a positive multiple of 64", nm);
 
   GemmParams p;
-  int span_max = 0;
-  int rc = build_structure(a, p, span_max);
+  int span_max = 0, span_w = 0;
+  // single-row kernels (1 x k, column stride 1): the k kernel columns share one staged halo box (SE_GEMM_WSHARE=0: off)
+  static const char* ws_env = getenv("SE_GEMM_WSHARE");
+  const bool wshare = !(ws_env && atoi(ws_env) == 0) && a->kh == 1 && a->kw > 1 && a->sw == 1 &&
+                      (!a->transposed || a->sh == 1);
+  int rc = build_structure(a, p, span_max, wshare, span_w);
   if (rc != SE_OK) return rc;
   const int npad = round_up(a->Cout2, 16);
   static const char* force = getenv("SE_GEMM_FORCE");       // "TW,nacc,mode" (tuning aid; mode 0 concat, 1 split, 2 split x2)
   static const char* dbg_env = getenv("SE_GEMM_DEBUG");     // bit2: print the plan of every launch
   const int dbg = dbg_env ? atoi(dbg_env) : 0;
-  TileChoice tc = choose_tile(a, p, span_max, npad);
+  TileChoice tc = choose_tile(a, p, span_max, npad, span_w);
   if (force) {
     int fTW = 0, fn = 0, fm = 0;
-    if (sscanf(force, "%d,%d,%d", &fTW, &fn, &fm) == 3 && fTW >= 8 && fTW <= 128 && fm >= 0 && fm <= 2 &&
+    if (span_w == 0 && sscanf(force, "%d,%d,%d", &fTW, &fn, &fm) == 3 && fTW >= 8 && fTW <= 128 && fm >= 0 && fm <= 2 &&
         (fm != 0 || npad <= 128) && (fm != 2 || (npad % 32 == 0 && npad >= 64))) {
       const int ac = fm == 0 ? 2 * npad : npad, ur = fm == 0 ? 2 * npad : npad / (fm == 2 ? 2 : 1);
       const int64_t as = 2LL * (fn * (128 / fTW) + span_max) * fTW * 128, bu = (int64_t)ur * 128;
@@ -821,7 +858,8 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   p.concat = concat ? 1 : 0; p.acc_cols = concat ? 2 * npad : npad;
   p.nsplit = tc.nsplit; p.unit_rows = concat ? 2 * npad : npad / tc.nsplit;
   const int rows = tc.nacc * tc.TH + span_max;
-  p.a_half = rows * tc.TW * 128; p.a_slot = 2 * p.a_half;
+  p.TWb = span_w > 0 ? round_up(tc.TW + span_w, 8) : tc.TW;
+  p.a_half = rows * p.TWb * 128; p.a_slot = 2 * p.a_half;
   p.b_unit = p.unit_rows * 128;
   p.SA = tc.SA; p.SB = tc.SB;
   p.Ho = a->Ho; p.Wo = a->Wo; p.Cout2 = a->Cout2; p.npad = npad; p.y_Cp = a->y_Cp;
@@ -881,7 +919,7 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     uint64_t dims[4] = {Cp, (uint64_t)sW, (uint64_t)sH, (uint64_t)(a->B * 2)};
     uint64_t str[3] = {Cp * 2, (uint64_t)a->src_Wpitch[j] * Cp * 2,
                        (uint64_t)a->src_Hpitch[j] * a->src_Wpitch[j] * Cp * 2};
-    uint32_t box[4] = {64, (uint32_t)(tc.TW * p.col_mul), (uint32_t)(rows * p.row_mul), 1};
+    uint32_t box[4] = {64, (uint32_t)(p.TWb * p.col_mul), (uint32_t)(rows * p.row_mul), 1};
     uint32_t es[4] = {1, (uint32_t)p.col_mul, (uint32_t)p.row_mul, 1};
     rc = make_tmap_bf16(&tmX[i], a->src[j], 4, dims, str, box, es, true);
     if (rc != SE_OK) return rc;
@@ -909,6 +947,7 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
     fprintf(stderr, "se_cconv_gemm: tr=%d Cp=%d+%d N=%d k=%dx%d s=%dx%d -> TH=%d TW=%d nacc=%d concat=%d nsplit=%d SA=%d SB=%d rows=%d smem=%d tmem=%d nbuf=%d tiles=%lld ncls=%d\n",
             a->transposed, a->src_Cp[0], a->nsrc == 2 ? a->src_Cp[1] : 0, npad, a->kh, a->kw, a->sh, a->sw, tc.TH, tc.TW,
             tc.nacc, p.concat, p.nsplit, tc.SA, tc.SB, rows, smem, p.tmem_cols, p.nbuf, (long long)ntiles, p.ncls);
+  if ((dbg & 4) && span_w > 0) fprintf(stderr, "se_cconv_gemm:   column-shared halo box: TWb=%d (span %d)\n", p.TWb, span_w);
   const unsigned grid = (unsigned)(ntiles < num_sms() ? ntiles : num_sms());
   static const char* prof_env = getenv("SE_GEMM_PROF");      // tuning aid: synchronous, prints per-role cycle counters
   p.prof = nullptr;

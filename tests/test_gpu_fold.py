@@ -115,3 +115,48 @@ def test_auto_mode_folds_the_layers_the_cost_model_names(monkeypatch):
     monkeypatch.setattr(chain, 'FOLD_MODE', 'auto')
     assert chain.FusedBlock(se.ComplexConv2d(128, 256, (5, 2), stride=(2, 1), padding=(2, 0))).fold is None
     assert chain.FusedBlock(mk(128, 32, (5, 2), (2, 1), (2, 0))).fold['kind'] == 'phase' 
+
+
+#             kind cin2 cout2 kernel stride padding  B  H   W   two   bias  pad_left
+ROW_CASES = [('C', 64, 64, (1, 7), (1, 1), (0, 3), 2, 5, 501, False, False, 0),      # DCUNet enc1
+             ('T', 128, 64, (1, 7), (1, 1), (0, 3), 2, 3, 300, True, False, 0),      # DCUNet dec8 (two sources)
+             ('C', 64, 128, (1, 2), (1, 1), (0, 0), 1, 4, 131, False, True, 1),      # causal pad: shifts 0 and 1
+             ('C', 128, 256, (1, 5), (1, 1), (0, 0), 2, 2, 77, False, False, 0),     # N = 256 (split operand form), W < 128
+             ('T', 64, 32, (1, 3), (1, 1), (0, 1), 3, 7, 129, False, True, 0),
+             ('C', 64, 48, (1, 9), (2, 1), (0, 4), 2, 9, 260, False, False, 0)]      # row stride 2, nine column shifts (> 8)
+
+
+@pytest.mark.parametrize('kind,cin2,cout2,k,s,p,B,H,W,two,bias,pad_left', ROW_CASES)
+def test_single_row_kernels_share_one_halo_box(kind, cin2, cout2, k, s, p, B, H, W, two, bias, pad_left, built_lib):
+    """1 x k kernels: the k kernel columns are column-shifted views of ONE staged A box (UMMA descriptors with a matrix
+    base offset) instead of k separate loads; against the fp64 oracle and the exact-fp32 SIMT engine"""
+    tr = kind == 'T'
+    mk = se.ComplexConvTranspose2d if tr else se.ComplexConv2d
+    m = mk(cin2, cout2, k, stride=s, padding=p, bias=bias)
+    sd = {kk: rand(v.shape, 180 + j, 0.1) for j, (kk, v) in enumerate(sorted(m.state_dict().items()))}
+    m.load_state_dict(sd)
+    m.to(DEV)
+    srcs_c = [cin2 // 2, cin2 // 2] if two else [cin2]
+    xs = [rand((B, c, H, W), 190 + i).to(DEV) for i, c in enumerate(srcs_c)]
+    full = se.complex_concat(xs, dim=1) if two else xs[0]
+    if pad_left:
+        full = torch.nn.functional.pad(full, (pad_left, 0, 0, 0))
+    rc, ic = m.real_conv, m.imag_conv
+    br, bi = (rc.bias.cpu().double(), ic.bias.cpu().double()) if bias else (None, None)
+    fd = full.cpu().double()
+    if tr:
+        want = oracle.cconvT2d_ref(fd, rc.weight.cpu().double(), ic.weight.cpu().double(), br, bi, s, p, (0, 0), (1, 1))
+    else:
+        want = oracle.cconv2d_ref(fd, rc.weight.cpu().double(), ic.weight.cpu().double(), br, bi, s, p, (1, 1))
+    with torch.no_grad():
+        blk = chain.FusedBlock(m, None, None, src_channels=srcs_c, concat='complex')
+        act, _ = blk([chain.cl2_from_nchw(x) for x in xs], pad_left=pad_left, out_cl2=True)
+        got = chain.cl2_to_nchw(act).cpu()
+        m.engine = 2                                           # module path on the tensor engine (NCHW in / out)
+        got_mod = m(full.contiguous()).cpu()
+        m.engine = 1                                           # exact fp32 SIMT
+        got_simt = m(full.contiguous()).cpu()
+    assert got.shape == want.shape
+    assert rel_l2(got_simt, want) < 1e-5
+    assert rel_l2(got, want) < 2e-4 and rel_l2(got_mod, want) < 2e-4
+    assert rel_l2(got, got_simt) < 5e-5
