@@ -136,7 +136,10 @@ cconv_first_kernel(const SmallCinParams p) {
   const int64_t b = blockIdx.y;
   if (pix0 >= plane) return;
 
-  float xk[PX][K];
+  // Packed FP32 (scripts/ffma2_rate.cu: a 3-register FFMA issues at 73 FMA lanes / clk / SM on B200, fma.rn.f32x2 at
+  // 113): two neighbouring output channels share one FFMA2 -- their weights are a natural register pair of the LDS.128,
+  // the input sample is kept as a (x, x) pair.  Per-lane arithmetic and order are those of the scalar loop.
+  float2 xk[PX][K];
   bool ok[PX];
 #pragma unroll
   for (int i = 0; i < PX; ++i) {
@@ -156,13 +159,14 @@ cconv_first_kernel(const SmallCinParams p) {
 #pragma unroll
         for (int dw = 0; dw < KW; ++dw) {
           const int w = w0 + dw;
-          xk[i][(c * KH + dh) * KW + dw] = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + dw) : 0.f;
+          const float v = (h_ok && w >= 0 && w < p.W) ? __ldg(xr + dw) : 0.f;
+          xk[i][(c * KH + dh) * KW + dw] = make_float2(v, v);
         }
       }
   }
   const float slope = p.slope;
   for (int c0 = 0; c0 < Cr; c0 += 32) {
-    float acc[PX][32];
+    float2 acc2[PX][16];
     {
       const float4* br = reinterpret_cast<const float4*>(b_s + c0);
 #pragma unroll
@@ -170,7 +174,8 @@ cconv_first_kernel(const SmallCinParams p) {
         const float4 b4 = br[j4];
 #pragma unroll
         for (int i = 0; i < PX; ++i) {
-          acc[i][4 * j4] = b4.x; acc[i][4 * j4 + 1] = b4.y; acc[i][4 * j4 + 2] = b4.z; acc[i][4 * j4 + 3] = b4.w;
+          acc2[i][2 * j4] = make_float2(b4.x, b4.y);
+          acc2[i][2 * j4 + 1] = make_float2(b4.z, b4.w);
         }
       }
     }
@@ -182,10 +187,8 @@ cconv_first_kernel(const SmallCinParams p) {
         const float4 w4 = wr[j4];
 #pragma unroll
         for (int i = 0; i < PX; ++i) {
-          acc[i][4 * j4 + 0] = fmaf(w4.x, xk[i][k], acc[i][4 * j4 + 0]);
-          acc[i][4 * j4 + 1] = fmaf(w4.y, xk[i][k], acc[i][4 * j4 + 1]);
-          acc[i][4 * j4 + 2] = fmaf(w4.z, xk[i][k], acc[i][4 * j4 + 2]);
-          acc[i][4 * j4 + 3] = fmaf(w4.w, xk[i][k], acc[i][4 * j4 + 3]);
+          acc2[i][2 * j4] = __ffma2_rn(make_float2(w4.x, w4.y), xk[i][k], acc2[i][2 * j4]);
+          acc2[i][2 * j4 + 1] = __ffma2_rn(make_float2(w4.z, w4.w), xk[i][k], acc2[i][2 * j4 + 1]);
         }
       }
     }
@@ -193,21 +196,24 @@ cconv_first_kernel(const SmallCinParams p) {
     for (int i = 0; i < PX; ++i) {
       if (!ok[i]) continue;
       const int64_t pix = pix0 + (int64_t)i * blockDim.x;
+      float acc_i[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) acc[i][j] = acc[i][j] > 0.f ? acc[i][j] : acc[i][j] * slope;
+      for (int j = 0; j < 16; ++j) { acc_i[2 * j] = acc2[i][j].x; acc_i[2 * j + 1] = acc2[i][j].y; }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc_i[j] = acc_i[j] > 0.f ? acc_i[j] : acc_i[j] * slope;
       if (p.y != nullptr) {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc[i][j];
+          if (c0 + j < p.Cout2) p.y[(b * p.Cout2 + c0 + j) * plane + pix] = acc_i[j];
       }
       if (p.y_cl2 != nullptr) {
         // channels >= Cout2 inside this pass carry zero weights and zero bias: they come out as exact zeros
         uint32_t hi[16], lo[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-          const __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[i][2 * j], acc[i][2 * j + 1]);
+          const __nv_bfloat162 h2 = __floats2bfloat162_rn(acc_i[2 * j], acc_i[2 * j + 1]);
           const float2 hf = __bfloat1622float2(h2);
-          const __nv_bfloat162 l2 = __floats2bfloat162_rn(acc[i][2 * j] - hf.x, acc[i][2 * j + 1] - hf.y);
+          const __nv_bfloat162 l2 = __floats2bfloat162_rn(acc_i[2 * j] - hf.x, acc_i[2 * j + 1] - hf.y);
           hi[j] = *reinterpret_cast<const uint32_t*>(&h2);
           lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
         }

@@ -26,8 +26,10 @@ namespace {
 
 constexpr int NFFT = 512;       // points of the complex FFT (= fft_size)
 constexpr int TILE = 32;        // frames (forward) / hop blocks (inverse) per CTA
-constexpr int THREADS = 256;
+constexpr int THREADS = 512;     // inverse kernel: 16 warps = the 16 frame pairs of a tile, one round
 constexpr int WARPS = THREADS / 32;
+constexpr int SROWS = 16 * 33;   // rows of the inverse kernel's tile: 2F = 514 spectrum rows, >= 16 * TPITCH so that a
+                                 // pair's own column doubles as its transpose scratch
 constexpr int ZPITCH = 529;     // float2 per pair row: >= 16*33 transpose scratch, odd -> conflict-free columns
 constexpr int TPITCH = 33;      // transpose scratch row pitch (float2)
 constexpr int MAXJ = 8;         // ceil(win / hop) covered by the inverse kernel
@@ -174,6 +176,46 @@ __device__ __forceinline__ void warp_fft512_emit(float2 (&v)[16], const float2* 
     float2 other = make_float2(__shfl_xor_sync(0xffffffffu, mine.x, 16), __shfl_xor_sync(0xffffffffu, mine.y, 16));
     emit(k_, make_float2(fmaf(sgn, mine.x, other.x), fmaf(sgn, mine.y, other.y)));   // E + O' (h = 0) / E - O' (h = 1)
   });
+}
+
+// warp_fft512 with the stage twiddles read from a shared-memory table tw_s[k2 * 32 + lane] and the transpose scratch
+// addressed with a stride: scratch element i lives at col[i * hp].  The inverse kernel passes the pair's own column of
+// the spectrum tile (already consumed into registers), so it needs no scratch buffer of its own.
+template <bool INV>
+__device__ __forceinline__ void warp_fft512_col(float2 (&v)[16], const float2* __restrict__ tw_s, float2* col, int hp,
+                                                int lane) {
+  fft16<INV>(v);
+  static_for<16>([&](auto k2_) {
+    constexpr int k2 = decltype(k2_)::value;
+    float2 y = v[brev4(k2)];
+    if constexpr (k2 != 0) {
+      const float2 t = tw_s[k2 * 32 + lane];
+      y = cmul_w<INV>(y, t.x, t.y);
+    }
+    col[(k2 * TPITCH + lane) * hp] = y;
+  });
+  __syncwarp();
+  const int h = lane >> 4, k2l = lane & 15;
+  static_for<16>([&](auto m_) {
+    constexpr int m = decltype(m_)::value;
+    v[m] = col[(k2l * TPITCH + 2 * m + h) * hp];
+  });
+  __syncwarp();
+  fft16<INV>(v);
+  float2 r[16];
+  const float sgn = h ? -1.0f : 1.0f;
+  static_for<16>([&](auto k_) {
+    constexpr int k = decltype(k_)::value;
+    float2 mine = v[brev4(k)];
+    if constexpr (k != 0) {                  // odd half: times W32^k before the last butterfly
+      float c = h ? cos32(k) : 1.0f, sn = h ? sin32(k) : 0.0f;
+      mine = cmul_w<INV>(mine, c, sn);
+    }
+    float2 other = make_float2(__shfl_xor_sync(0xffffffffu, mine.x, 16), __shfl_xor_sync(0xffffffffu, mine.y, 16));
+    r[k] = make_float2(fmaf(sgn, mine.x, other.x), fmaf(sgn, mine.y, other.y));   // E + O' (h = 0) / E - O' (h = 1)
+  });
+  static_for<16>([&](auto k_) {
+    constexpr int k = decltype(k_)::value; v[k] = r[k]; });
 }
 
 __device__ __forceinline__ void lane_twiddles(float2 (&tw)[16], int lane) {
@@ -383,19 +425,20 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
                  TOut* __restrict__ out, int Q, int tq, int tiles, int total, unsigned hop_magic) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int F = NFFT / 2 + 1, C2 = 2 * F;
-  float* sbuf = reinterpret_cast<float*>(smem_raw);                         // [C2][IPITCH]: spectra, then frames
-  float2* scratch = reinterpret_cast<float2*>(sbuf + (size_t)C2 * IPITCH);  // [WARPS][16 * TPITCH]
+  float* sbuf = reinterpret_cast<float*>(smem_raw);                         // [SROWS][IPITCH]: spectra, then frames
+  float2* tw_s = reinterpret_cast<float2*>(sbuf + (size_t)SROWS * IPITCH);  // [16][32] stage twiddles (cos, sin magnitudes)
+  float* wl_s = reinterpret_cast<float*>(tw_s + 16 * 32);                   // [NFFT] window / N (0 beyond win)
   const int tid = threadIdx.x, lane = tid & 31, warp = uniform_warp_idx();
 
-  float2 tw[16];
-  lane_twiddles(tw, lane);
+  // 64 registers per thread (32 resident warps per SM instead of 16): the stage twiddles and the window taps live in
+  // shared-memory tables, and a pair's transpose scratch is its own column of the tile
+  for (int i = tid; i < 16 * 32; i += THREADS) {
+    float sn, cs;
+    sincospif((float)((i >> 5) * (i & 31)) * (1.0f / 256.0f), &sn, &cs);      // angle 2 pi lane k2 / 512
+    tw_s[i] = make_float2(cs, sn);
+  }
+  for (int i = tid; i < NFFT; i += THREADS) wl_s[i] = i < win ? __ldg(window + i) * (1.0f / NFFT) : 0.0f;
   const int h = lane >> 4, m2 = lane & 15;
-  float wl[16];
-  static_for<16>([&](auto k_) {
-    constexpr int k = decltype(k_)::value;
-    int m = 16 * k + 256 * h + m2;
-    wl[k] = m < win ? __ldg(window + m) * (1.0f / NFFT) : 0.0f;
-  });
   const float cpar = (m2 & 1) ? c_odd : c_even;
   constexpr int hp = IPITCH >> 1;                              // row pitch in float2 (odd)
   float2* s2 = reinterpret_cast<float2*>(sbuf);
@@ -455,8 +498,8 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
         }
         v[f2] = gg;
       });
-      __syncwarp();
-      warp_fft512<true>(v, tw, scratch + warp * (16 * TPITCH), lane);
+      __syncwarp();                                      // every lane holds its share of the column: it is scratch now
+      warp_fft512_col<true>(v, tw_s, s2 + p, hp, lane);
       // rank-2 term of the truncated-DFT pseudo-inverse: subtract c_parity * (sum of this parity's samples below win)
       float2 acc = make_float2(0.f, 0.f);
       static_for<16>([&](auto k_) {
@@ -470,10 +513,13 @@ istft_fft_kernel(const float* __restrict__ spec, int T, const float* __restrict_
       }
       acc.x *= cpar; acc.y *= cpar;
       // rows >= win get zeros (their window tap is 0); the overlap-add never reads them
+      __syncwarp();                                      // the scratch reads of the other lanes are done
       float2* ycol = s2 + p + (256 * h + m2) * hp;
+      const float* wlp = wl_s + 256 * h + m2;
       static_for<16>([&](auto k_) {
         constexpr int k = decltype(k_)::value;
-        ycol[16 * k * hp] = make_float2((v[k].x - acc.x) * wl[k], (v[k].y - acc.y) * wl[k]);
+        const float w = wlp[16 * k];
+        ycol[16 * k * hp] = make_float2((v[k].x - acc.x) * w, (v[k].y - acc.y) * w);
       });
     }
     __syncthreads();
@@ -561,7 +607,7 @@ int istft_fft_launch(const char* nm, const float* spec, int64_t B, int64_t T, co
   int tq = TILE - halo;                                       // hop blocks of output per tile (32 frames with the halo)
   int64_t tiles = (Q + tq - 1) / tq;
   SE_REQUIRE(tiles * B < (1ll << 31), "%s: batch x frame count too large", nm);
-  size_t smem = (size_t)(fft + 2) * IPITCH * sizeof(float) + (size_t)WARPS * 16 * TPITCH * sizeof(float2);
+  size_t smem = (size_t)SROWS * IPITCH * sizeof(float) + 16 * 32 * sizeof(float2) + NFFT * sizeof(float);
   static se::PerDevice<bool> attr_set_pd(false);
   bool& attr_set = attr_set_pd.get();
   if (!attr_set) {
