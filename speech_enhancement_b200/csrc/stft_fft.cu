@@ -61,8 +61,14 @@ __host__ __device__ constexpr float sin32(int j) {
   return t[j];
 }
 
+// complex add / subtract as ONE packed add.f32x2 each (sm_100 FADD2): the butterflies are half of the FFT's FP instructions
+#ifdef SE_FFT_SCALAR_ADDS
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+#else
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }
+#endif
 // a * (c - i s) forward, a * (c + i s) inverse
 template <bool INV>
 __device__ __forceinline__ float2 cmul_w(float2 a, float c, float s) {
