@@ -200,6 +200,9 @@ typedef struct se_cconv_args {
    * forward / stride-1 layer (k + s taps of 2 N columns instead of 2 k taps of N): complex_nn.py:67-91 layers with few
    * output channels, where every 128-row MMA is bound by its A-operand read, not by N.                              */
   int fold_h, fold_w, fold_cg, fold_cout2;
+  /* with folding: the launch covers only the output pixels (out_h_add + i * out_h_mul, out_w_add + j * out_w_mul)
+   * (0 = every pixel: mul 1, add 0) -- an axis whose phases are NOT folded is served by one launch per phase */
+  int out_h_mul, out_h_add, out_w_mul, out_w_add;
 } se_cconv_args;
 SE_API int se_cl2_from_nchw(const float* x, int64_t B, int C, int H, int W, void* cl2, int Cp, void* stream);
 /* fp32 x[b*xs_b + c*xs_c + h*xs_h + w] -> CL2 (same as se_cl2_from_nchw for arbitrary outer strides). */

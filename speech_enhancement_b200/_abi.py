@@ -91,7 +91,8 @@ class ConvArgs(C.Structure):
                 ('y_bs', C.c_int64), ('y_cs', C.c_int64), ('y_hs', C.c_int64), ('y_ws', C.c_int64),
                 ('y_off', C.c_int64), ('y_lim', C.c_int64), ('y_scale', C.c_void_p),
                 ('src_H', C.c_int * 2), ('src_W', C.c_int * 2), ('src_C', C.c_int * 2),
-                ('fold_h', C.c_int), ('fold_w', C.c_int), ('fold_cg', C.c_int), ('fold_cout2', C.c_int)]
+                ('fold_h', C.c_int), ('fold_w', C.c_int), ('fold_cg', C.c_int), ('fold_cout2', C.c_int),
+                ('out_h_mul', C.c_int), ('out_h_add', C.c_int), ('out_w_mul', C.c_int), ('out_w_add', C.c_int)]
 
 
 _lib = None

@@ -213,18 +213,38 @@ class FusedBlock:
         self.fold = None
         if self.transposed and not self.scatter_form and self.sh * self.sw > 1 and FOLD_MODE != '0':
             oh, ow = _phase_offsets(self.kh, self.sh, self.ph), _phase_offsets(self.kw, self.sw, self.pw)
-            es = sorted({e for v in oh.values() for _, e in v})
-            fs = sorted({f for v in ow.values() for _, f in v})
             cg = (self.cout2 + 31) // 32 * 32
-            nph = self.sh * self.sw
-            if es and fs and nph * cg <= 256 and len(es) * len(fs) <= 49:
-                # 'auto' keeps to the concat operand form (<= 128 folded columns): measured on DCUNet dec7 (4 phases x
-                # 64 = 256 columns, split form) the folded launch LOSES, 6.97 -> 9.98 ms, although the MMA model favours it
-                es, fs = list(range(es[0], es[-1] + 1)), list(range(fs[0], fs[-1] + 1))   # contiguous offset window
-                gain = (self.kh * self.kw * _mma_cost((self.cout2 + 15) // 16 * 16)
-                        / (len(es) * len(fs) * _mma_cost(nph * cg)))
-                if FOLD_MODE == '1' or (gain > 1.1 and nph * cg <= 128):
-                    self.fold = dict(kind='phase', oh=oh, ow=ow, es=es, fs=fs, cg=cg, nph=nph, gain=gain)
+            unfolded = self.kh * self.kw * _mma_cost((self.cout2 + 15) // 16 * 16)
+            best = None
+            # fold both axes, or only one (the other axis' phases then get one launch each).  'auto' keeps to the concat
+            # operand form (<= 128 folded columns): measured on DCUNet dec7 (4 phases x 64 = 256 columns, split form) the
+            # fully folded launch LOSES, 6.97 -> 9.98 ms (weight-slab fill bound), although the MMA model favours it
+            for fh, fw in ((self.sh, self.sw), (self.sh, 1), (1, self.sw)):
+                if fh * fw <= 1 or fh * fw * cg > 256:
+                    continue
+                launches, cost = [], 0.0
+                for rh in ([None] if fh > 1 or self.sh == 1 else range(self.sh)):
+                    for rw in ([None] if fw > 1 or self.sw == 1 else range(self.sw)):
+                        poh = oh if rh is None else {0: oh[rh]}
+                        pow_ = ow if rw is None else {0: ow[rw]}
+                        es = sorted({e for v in poh.values() for _, e in v})
+                        fs = sorted({f for v in pow_.values() for _, f in v})
+                        if not es or not fs:
+                            launches = None            # a phase no tap reaches (kernel smaller than the stride): not folded
+                            break
+                        es, fs = list(range(es[0], es[-1] + 1)), list(range(fs[0], fs[-1] + 1))
+                        launches.append(dict(rh=rh, rw=rw, oh=poh, ow=pow_, es=es, fs=fs))
+                        cost += len(es) * len(fs) * _mma_cost(fh * fw * cg)
+                    if launches is None:
+                        break
+                if not launches or any(len(l['es']) * len(l['fs']) > 49 for l in launches):
+                    continue
+                gain = unfolded / cost                # both per pixel of the full quotient grid (sh * sw output pixels)
+                if FOLD_MODE != '1' and (gain <= 1.1 or fh * fw * cg > 128):
+                    continue
+                if best is None or gain > best['gain']:
+                    best = dict(kind='phase', fh=fh, fw=fw, cg=cg, nph=fh * fw, launches=launches, gain=gain)
+            self.fold = best
         # narrow layers WITHOUT output phases (forward convolutions, stride-1 transposed ones): two adjacent output
         # pixels along one axis share a GEMM row -- that axis is walked at twice the stride with k + s taps, the two
         # pixels are two column groups (N = 2 x channels).  k taps of N columns per pixel become (k + s) / 2 of 2 N.
@@ -303,20 +323,24 @@ class FusedBlock:
                 cg, nph = f['cg'], f['nph']
                 p4 = packed.view(2 * co, 2 * ci, kh, kw)
                 if f['kind'] == 'phase':
-                    wf = fold_transposed_weight(p4, self.sh, self.sw, f)
+                    # one operand per launch: the phases of a folded axis side by side, one phase of an unfolded axis
+                    wfs = [fold_transposed_weight(p4, f['fh'], f['fw'], dict(l, cg=cg, nph=nph)) for l in f['launches']]
                 else:
                     if self.transposed:       # stride-1 transposed convolution = forward convolution with flipped taps
                         p4 = p4.flip(2, 3)
-                    wf = fold_pixel_pairs_weight(p4, f['axis'], self.sh if f['axis'] == 0 else self.sw, cg)
-                ntap = wf.shape[2] * wf.shape[3]
-                wf = wf.reshape(nph * cg, 2 * ci * ntap).contiguous()
+                    wfs = [fold_pixel_pairs_weight(p4, f['axis'], self.sh if f['axis'] == 0 else self.sw, cg)]
                 bias_fold = torch.zeros((nph, cg), device=dev, dtype=torch.float32)
                 bias_fold[:, :2 * co] = bias
                 bias_fold = bias_fold.reshape(-1).contiguous()
-                wq_fold = torch.empty((lib.se_cconv_wq_elems(nph * cg, cpt, ntap),), device=dev, dtype=torch.bfloat16)
-                with torch.cuda.device(dev):
-                    _abi.check(lib.se_cconv_prep_weight(_abi.ptr(wf), nph * cg, 2 * ci, ntap, _abi.ptr(cmap_t), cpt,
-                                                        _abi.ptr(wq_fold), _abi.stream_ptr()))
+                wq_fold = []
+                for wf in wfs:
+                    ntap = wf.shape[2] * wf.shape[3]
+                    wf = wf.reshape(nph * cg, 2 * ci * ntap).contiguous()
+                    wq_f = torch.empty((lib.se_cconv_wq_elems(nph * cg, cpt, ntap),), device=dev, dtype=torch.bfloat16)
+                    with torch.cuda.device(dev):
+                        _abi.check(lib.se_cconv_prep_weight(_abi.ptr(wf), nph * cg, 2 * ci, ntap, _abi.ptr(cmap_t), cpt,
+                                                            _abi.ptr(wq_f), _abi.stream_ptr()))
+                    wq_fold.append(wq_f)
         self._ops = {'packed': packed, 'bias': bias, 'slope': slope, 'wq': wq, 'cpt': cpt, 'wq_sc': wq_sc,
                      'wq_fold': wq_fold, 'bias_fold': bias_fold}
         self._key = key
@@ -392,25 +416,34 @@ class FusedBlock:
             return None, y
         if self.fold is not None and y is None and y_act is not None:
             f = self.fold
-            if f['kind'] == 'phase':
-                # phase-folded form: stride-1 forward convolution over the input grid, phases as column groups
-                a.transposed, a.kh, a.kw, a.sh, a.sw = 0, len(f['es']), len(f['fs']), 1, 1
-                a.ph, a.pw = -f['es'][0], -f['fs'][0]
-                a.fold_h, a.fold_w = self.sh, self.sw
-            else:
-                # pixel-pair form: the folded axis is walked at twice the stride with k + s taps
-                kh, kw, sh, sw, ph, pw = self.kh, self.kw, self.sh, self.sw, self.ph, self.pw
-                if self.transposed:           # forward equivalent of a stride-1 transposed convolution
-                    ph, pw = kh - 1 - ph, kw - 1 - pw
-                a.transposed = 0
-                if f['axis'] == 0:
-                    a.kh, a.kw, a.sh, a.sw, a.fold_h, a.fold_w = kh + sh, kw, 2 * sh, sw, 2, 1
-                else:
-                    a.kh, a.kw, a.sh, a.sw, a.fold_h, a.fold_w = kh, kw + sw, sh, 2 * sw, 1, 2
-                a.ph, a.pw = ph, pw
+            a.transposed = 0
             a.Cout2 = f['nph'] * f['cg']
             a.fold_cg, a.fold_cout2 = f['cg'], self.cout2
-            a.wq, a.bias = ops['wq_fold'].data_ptr(), ops['bias_fold'].data_ptr()
+            a.bias = ops['bias_fold'].data_ptr()
+            if f['kind'] == 'phase':
+                # phase-folded form: stride-1 forward convolution(s) over the input grid, the phases of the folded axes as
+                # column groups; an unfolded axis with stride > 1 gets one launch per phase, each covering every s-th row /
+                # column of the output
+                a.sh, a.sw, a.fold_h, a.fold_w = 1, 1, f['fh'], f['fw']
+                with torch.cuda.device(dev), _abi.stage('cconv'):
+                    for l, wq_f in zip(f['launches'], ops['wq_fold']):
+                        a.kh, a.kw = len(l['es']), len(l['fs'])
+                        a.ph, a.pw = -l['es'][0], -l['fs'][0]
+                        a.out_h_mul, a.out_h_add = (self.sh, l['rh']) if l['rh'] is not None else (0, 0)
+                        a.out_w_mul, a.out_w_add = (self.sw, l['rw']) if l['rw'] is not None else (0, 0)
+                        a.wq = wq_f.data_ptr()
+                        _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
+                return y_act, y
+            # pixel-pair form: the folded axis is walked at twice the stride with k + s taps
+            kh, kw, sh, sw, ph, pw = self.kh, self.kw, self.sh, self.sw, self.ph, self.pw
+            if self.transposed:           # forward equivalent of a stride-1 transposed convolution
+                ph, pw = kh - 1 - ph, kw - 1 - pw
+            if f['axis'] == 0:
+                a.kh, a.kw, a.sh, a.sw, a.fold_h, a.fold_w = kh + sh, kw, 2 * sh, sw, 2, 1
+            else:
+                a.kh, a.kw, a.sh, a.sw, a.fold_h, a.fold_w = kh, kw + sw, sh, 2 * sw, 1, 2
+            a.ph, a.pw = ph, pw
+            a.wq = ops['wq_fold'][0].data_ptr()
         with torch.cuda.device(dev), _abi.stage('cconv'):
             _abi.check(_abi.lib().se_cconv_gemm(C.byref(a), _abi.stream_ptr()))
         return y_act, y

@@ -61,6 +61,7 @@ struct GemmParams {
   // (qh * fold_h + r, qw * fold_w + s).  Cg = accumulator columns per phase, Cout2g = real channels per phase.
   // Not folded: fold_h = fold_w = 1, Cg = npad, Cout2g = Cout2.
   int fold_h, fold_w, Cg, Cout2g;
+  int ph_h_mul, ph_w_mul;     // output distance between neighbouring folded phases (1 unless the launch covers a sub-grid)
   const float* bias;
   float slope;
   float* y;
@@ -445,7 +446,7 @@ cconv_gemm_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constan
             cc = (g - ph * cpp) << 5;
             tcol = ph * Cg + cc;
             const int r = ph / p.fold_w;
-            ho = ho0 + r; wo = wo0 + (ph - r * p.fold_w);
+            ho = ho0 + r * p.ph_h_mul; wo = wo0 + (ph - r * p.fold_w) * p.ph_w_mul;
             ok = q_ok && ho < p.Ho && wo < p.Wo;
             ypos = (int64_t)wo * p.y_ws;
             yb = do_f32 ? p.y + b * p.y_bs + (int64_t)ho * p.y_hs + p.y_off + ypos : nullptr;
@@ -627,8 +628,10 @@ static int build_structure(const se_cconv_args* a, GemmParams& p, int& span_max,
       } else {
         // folded launch: the M dimension walks the quotient grid, the column groups are the output phases
         const int fh = a->fold_h > 1 ? a->fold_h : 1, fw = a->fold_w > 1 ? a->fold_w : 1;
-        c.Hq_out = (a->Ho + fh - 1) / fh; c.Wq_out = (a->Wo + fw - 1) / fw;
-        c.oh_mul = fh; c.oh_add = 0; c.ow_mul = fw; c.ow_add = 0;
+        const int hm = a->out_h_mul > 1 ? a->out_h_mul : 1, wm = a->out_w_mul > 1 ? a->out_w_mul : 1;
+        c.oh_mul = fh * hm; c.oh_add = a->out_h_add; c.ow_mul = fw * wm; c.ow_add = a->out_w_add;
+        c.Hq_out = a->Ho > c.oh_add ? (a->Ho - c.oh_add + c.oh_mul - 1) / c.oh_mul : 0;
+        c.Wq_out = a->Wo > c.ow_add ? (a->Wo - c.ow_add + c.ow_mul - 1) / c.ow_mul : 0;
       }
       if (c.Hq_out <= 0 || c.Wq_out <= 0) continue;
       c.g0 = ng; c.ng = 0;
@@ -815,6 +818,10 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   if (a->B > 32767) return fail(SE_ERR_UNSUPPORTED, "%s: batch too large", nm);
   if (a->transposed && (a->pad_top || a->pad_left))
     return fail(SE_ERR_UNSUPPORTED, "%s: pad_top/pad_left only for the forward convolution", nm);
+  if ((a->out_h_mul > 1 || a->out_w_mul > 1 || a->out_h_add || a->out_w_add) &&
+      (a->transposed || a->out_h_add < 0 || a->out_w_add < 0 || a->out_h_add >= (a->out_h_mul > 1 ? a->out_h_mul : 1) ||
+       a->out_w_add >= (a->out_w_mul > 1 ? a->out_w_mul : 1)))
+    return fail(SE_ERR_BAD_ARG, "%s: out_*_mul / out_*_add describe a sub-grid of a forward launch, 0 <= add < mul", nm);
   if (a->fold_h > 1 || a->fold_w > 1) {
     const int nph = (a->fold_h > 1 ? a->fold_h : 1) * (a->fold_w > 1 ? a->fold_w : 1);
     if (a->transposed || a->fold_cg <= 0 || a->fold_cg % 32 != 0 ||
@@ -867,6 +874,7 @@ int cconv_gemm_launch(const se_cconv_args* a, cudaStream_t s) {
   p.fold_h = a->fold_h > 1 ? a->fold_h : 1; p.fold_w = a->fold_w > 1 ? a->fold_w : 1;
   p.Cg = folded ? a->fold_cg : npad;
   p.Cout2g = folded ? a->fold_cout2 : a->Cout2;
+  p.ph_h_mul = a->out_h_mul > 1 ? a->out_h_mul : 1; p.ph_w_mul = a->out_w_mul > 1 ? a->out_w_mul : 1;
   // TMEM: nacc accumulators per buffer; two buffers when they fit (epilogue overlaps the next tile's MMAs)
   const int tm_one = (tc.nacc - 1) * p.acc_cols + (concat ? npad : 0) + round_up(npad, 32);
   p.buf_cols = round_up(tc.nacc * p.acc_cols, 32);

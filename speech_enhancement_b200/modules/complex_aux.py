@@ -81,20 +81,43 @@ def lstm_pair_forward(owner, lstms, x, engine):
                     _abi.ptr(pre), pre.stride(0), _abi.ptr(_lstm_layer_params(lstms[0], 0)[1].contiguous()),
                     _abi.ptr(_lstm_layer_params(lstms[1], 0)[1].contiguous()), N, T, H, _abi.ptr(first[0]),
                     _abi.ptr(first[1]), _abi.stream_ptr()))
-        for i, m in enumerate(lstms):
-            h = first[i] if first is not None else _lstm_rec(pre, i * 4 * H, _lstm_layer_params(m, 0)[1], N, T, H)
-            for layer in range(1, L):
+        hs = [first[i] if first is not None else _lstm_rec(pre, i * 4 * H, _lstm_layer_params(m, 0)[1], N, T, H)
+              for i, m in enumerate(lstms)]
+        for layer in range(1, L):
+            if len(lstms) == 2 and engine == 'umma':
+                # deeper layers of the two LSTMs (FRCRN: ComplexLSTM(num_layers=2), _2206_07293_frcrn.py:113) read different
+                # inputs -- each its own previous layer -- so their projections fill the two column halves of ONE pre-gate
+                # matrix and both time loops again share a launch (twice the CTAs per launch at half-empty batches)
+                from ..chain import linear_many
+                pl = torch.empty((N * T, 2 * 4 * H), device=dev, dtype=torch.float32)
+                jobs = []
+                for i, m in enumerate(lstms):
+                    op = cache.get((i, layer))
+                    if op is None:
+                        op = cache[(i, layer)] = LinearOperand(
+                            lambda m=m, layer=layer: [(_lstm_layer_params(m, layer)[0], _lstm_layer_params(m, layer)[2])])
+                    jobs.append((op, hs[i].reshape(N * T, H), pl, i * 4 * H))
+                linear_many(jobs)
+                nxt = [torch.empty((N, T, H), device=dev, dtype=torch.float32) for _ in lstms]
+                with _abi.stage('lstm'):
+                    _abi.check(_abi.lib().se_lstm_rec_pair_fwd(
+                        _abi.ptr(pl), pl.stride(0), _abi.ptr(_lstm_layer_params(lstms[0], layer)[1].contiguous()),
+                        _abi.ptr(_lstm_layer_params(lstms[1], layer)[1].contiguous()), N, T, H, _abi.ptr(nxt[0]),
+                        _abi.ptr(nxt[1]), _abi.stream_ptr()))
+                hs = nxt
+                continue
+            for i, m in enumerate(lstms):
                 w_ih, w_hh, bias = _lstm_layer_params(m, layer)
                 if engine == 'umma':
                     op = cache.get((i, layer))
                     if op is None:
                         op = cache[(i, layer)] = LinearOperand(
                             lambda m=m, layer=layer: [(_lstm_layer_params(m, layer)[0], _lstm_layer_params(m, layer)[2])])
-                    pl = op(h.reshape(N * T, H))
+                    pl = op(hs[i].reshape(N * T, H))
                 else:
-                    pl = F.linear(h.reshape(N * T, H), w_ih, sum(bias) if bias else None)
-                h = _lstm_rec(pl, 0, w_hh, N, T, H)
-            outs.append(h)
+                    pl = F.linear(hs[i].reshape(N * T, H), w_ih, sum(bias) if bias else None)
+                hs[i] = _lstm_rec(pl, 0, w_hh, N, T, H)
+        outs = hs
     return outs
 
 

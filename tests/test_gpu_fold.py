@@ -19,7 +19,9 @@ CASES = [(128, 32, (5, 2), (2, 1), (2, 0), (1, 0), 2, 64, 70, True, False),     
          (64, 48, (3, 3), (2, 2), (0, 0), (1, 1), 1, 7, 11, False, True),       # no padding: offsets start below zero
          (32, 90, (5, 3), (2, 1), (2, 1), (0, 0), 2, 6, 13, False, False),      # 90 channels (DCUNet-large pads to 192)
          (64, 16, (4, 4), (2, 2), (1, 1), (0, 0), 2, 8, 8, False, True),        # even kernel
-         (64, 32, (2, 3), (3, 1), (0, 1), (2, 0), 2, 5, 9, False, False)]       # kernel smaller than the stride
+         (64, 32, (2, 3), (3, 1), (0, 1), (2, 0), 2, 5, 9, False, False),       # kernel smaller than the stride
+         (64, 128, (5, 3), (2, 2), (2, 1), (0, 0), 2, 9, 12, False, True),      # 128 channels: only ONE axis fits 256 columns
+         (128, 64, (7, 5), (2, 2), (3, 2), (1, 1), 1, 12, 10, True, False)]     # output_padding on both axes
 
 
 @pytest.mark.parametrize('cin2,cout2,k,s,p,op,B,H,W,two,bias', CASES)
@@ -40,8 +42,8 @@ def test_folded_block_matches_per_tap_form_and_oracle(cin2, cout2, k, s, p, op, 
     for mode in ('0', '1'):
         monkeypatch.setattr(chain, 'FOLD_MODE', mode)
         blk = chain.FusedBlock(m, None, torch.nn.LeakyReLU(0.2), src_channels=srcs_c, concat='complex')
-        nph_cols = s[0] * s[1] * ((cout2 + 31) // 32 * 32)
-        assert (blk.fold is not None) == (mode == '1' and nph_cols <= 256)
+        one_axis_cols = min(v for v in (s[0], s[1], s[0] * s[1]) if v > 1) * ((cout2 + 31) // 32 * 32)
+        assert (blk.fold is not None) == (mode == '1' and one_axis_cols <= 256)
         with torch.no_grad():
             act, _ = blk([chain.cl2_from_nchw(x) for x in xs], out_cl2=True)
             # poison check for the pad channels: consumers may read them (they must be exact zeros)
@@ -104,7 +106,8 @@ def test_auto_mode_folds_the_layers_the_cost_model_names(monkeypatch):
     assert chain.FusedBlock(mk(128, 32, (5, 2), (2, 1), (2, 0))).fold is not None      # DCCRN dec4
     assert chain.FusedBlock(mk(256, 64, (5, 2), (2, 1), (2, 0))).fold is not None      # DCCRN dec3
     assert chain.FusedBlock(mk(512, 128, (5, 2), (2, 1), (2, 0))).fold is None         # N = 256 already
-    assert chain.FusedBlock(mk(256, 64, (7, 5), (2, 2), (3, 2))).fold is None          # DCUNet dec7: 256 columns lose
+    f = chain.FusedBlock(mk(256, 64, (7, 5), (2, 2), (3, 2))).fold                      # DCUNet dec7: all 4 phases = 256
+    assert f is not None and (f['fh'], f['fw']) == (2, 1) and len(f['launches']) == 2   # columns lose; H only, 2 launches
     assert chain.FusedBlock(mk(256, 128, (5, 2), (2, 1), (0, 0))).fold is None         # FRCRN decoder
     # pixel-pair folding measured no gain on the short-K layers it applies to: built only under SE_CONV_FOLD=1
     assert chain.FusedBlock(mk(128, 64, (1, 7), (1, 1), (0, 3))).fold is None           # DCUNet dec8: stride 1, no phases
