@@ -20,7 +20,8 @@ path).  Rank 0 prints ONE JSON line (contract in the task statement):
                 model class staged in oracle/_ref; kind "port" when that directory is absent)
   other_configs the other BASELINE.json configurations in compact form (same protocol): DCCRN-CL at batch 1
                 (latency, eager and CUDA-graph replay), DCUNet-20 64 x 4 s, FRCRN 128 x 4 s over the GPUs of
-                the run, CARN training step global batch 32 over the GPUs of the run
+                the run, CARN training step global batch 32 over the GPUs of the run, and a sample of the
+                ConvSTFT -> ConviSTFT round-trip sweep (4 s x 256, 60 s x 8; both framings)
 The model timed on the GPU is the reference's own class (oracle/_ref, unmodified) bound to this package by
 dropin.install() + dropin.accelerate() when oracle/_ref is staged, else the package's host model
 (speech_enhancement_b200.callers); `config.gpu_model` says which.
@@ -651,6 +652,59 @@ def bench_train(steps, warmup, D, full=True):
     return res
 
 
+def bench_stft_roundtrip(steps, D):
+    """BASELINE configs[4]: ConvSTFT -> ConviSTFT round trip (win 400 / 512, hop 100 / 128, fft 512) on clips of 1-60 s.
+    A compact sample of the sweep (the full grid is profiles/r2_stft_roundtrip_sweep.txt): GB/s against algorithmic bytes
+    8 (L + C2 T) per clip, with the L2 flushed between calls; parity = the reference's own ConvSTFT / ConviSTFT on the CPU."""
+    import speech_enhancement_b200 as se
+    if D.rank != 0:
+        return None
+    dev = D.dev
+    pk = peaks()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    rows = []
+    for (win, hop), (sec, B) in (((400, 100), (4, 256)), ((400, 100), (60, 8)), ((512, 128), (4, 256)), ((512, 128), (60, 8))):
+        Ls = sec * SR
+        st, ist = se.ConvSTFT(win, hop, 512).to(dev), se.ConviSTFT(win, hop, 512).to(dev)
+        x = torch.randn(B, Ls, device=dev) * 0.1
+        with torch.no_grad():
+            for _ in range(2):
+                wav = ist(st(x))
+            ts = []
+            for _ in range(max(steps, 3)):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                spec = st(x)
+                wav = ist(spec)
+                e1.record()
+                torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        ms = ts[len(ts) // 2]
+        byt = 4 * (x.numel() + 2 * spec.numel() + wav.numel())
+        n = wav.shape[1]
+        row = {'framing': f'{win}/{hop}/512', 'clip_s': sec, 'batch': B, 'ms': ms, 'GB/s': byt / ms / 1e6,
+               'frac_hbm': byt / ms / 1e6 / pk['hbm_gbs'], 'audio_s_per_s': B * sec / (ms / 1e3),
+               'roundtrip_rel_l2': rel_l2(wav[:2].cpu(), x[:2, :n].cpu())}
+        if sec == 4 and reference_staged():
+            from oracle import ref_loader
+            ref = ref_loader.load_original()
+            with torch.no_grad():
+                rs, ri = ref.ConvSTFT(win, hop, 512), ref.ConviSTFT(win, hop, 512)
+                spec_c = rs(x[:2].cpu())
+                row['stft_rel_l2_vs_reference'] = rel_l2(spec[:2].cpu(), spec_c)
+                row['istft_rel_l2_vs_reference'] = rel_l2(ist(spec_c.to(dev)).cpu(), ri(spec_c))
+        rows.append(row)
+        del st, ist, x, spec, wav
+    ok = all(r['roundtrip_rel_l2'] < 1e-5 and r.get('stft_rel_l2_vs_reference', 0) < 1e-5
+             and r.get('istft_rel_l2_vs_reference', 0) < 1e-5 for r in rows)
+    return {'workload': 'ConvSTFT -> ConviSTFT round trip (BASELINE configs[4] sample: 4 s x 256 and 60 s x 8 clips, '
+                        'win 400 / hop 100 and win 512 / hop 128, fft 512), L2 flushed between calls',
+            'metric': 'stft_roundtrip_GB_per_s', 'rows': rows, 'roofline': {'bound': 'hbm', 'peak': pk['hbm_gbs'], 'unit': 'GB/s'},
+            'parity': {'ok': bool(ok), 'tolerance': {'rel_l2': 1e-5}, 'vs': 'reference' if reference_staged() else 'round trip'}}
+
+
 def compact(r):
     """other_configs entry: {workload, value, e2e, ms_per_step, roofline.frac, parity} (+ what identifies the run)"""
     if r is None:
@@ -707,6 +761,13 @@ def run_ours(args):
                 continue
             if D.rank == 0:
                 others.append(compact(r))
+    if args.others and key == 'dccrn':
+        try:
+            rt = bench_stft_roundtrip(min(args.steps, 10), D)
+        except Exception as e:
+            rt = {'workload': 'stft round trip', 'error': f'{type(e).__name__}: {e}'[:300]} if D.rank == 0 else None
+        if rt is not None:
+            others.append(rt)
     if D.rank != 0:
         D.close()
         return 0
