@@ -35,8 +35,9 @@ def _prep_wq(packed, cout2, cin2, taps, Cp):
     """packed fp32 [cout2][cin2][taps] -> bf16 hi|lo GEMM operand (se_cconv_prep_weight)."""
     n = _abi.lib().se_cconv_wq_elems(cout2, Cp, taps)
     wq = torch.empty(n, device=packed.device, dtype=torch.bfloat16)
-    _abi.check(_abi.lib().se_cconv_prep_weight(_abi.ptr(packed), cout2, cin2, taps, None, Cp, _abi.ptr(wq),
-                                               _abi.stream_ptr()))
+    with torch.cuda.device(packed.device):          # launches go on the current stream of the TENSOR's device
+        _abi.check(_abi.lib().se_cconv_prep_weight(_abi.ptr(packed), cout2, cin2, taps, None, Cp, _abi.ptr(wq),
+                                                   _abi.stream_ptr()))
     return wq
 
 
@@ -421,8 +422,9 @@ class ConviSTFT(_abi.InvalidatesCaches, nn.Module):
             c2, _, win = w.shape
             J = -(-win // self.hop_size)
             packed = torch.empty((self.hop_size, J * c2), device=w.device, dtype=torch.float32)
-            _abi.check(_abi.lib().se_istft_pack_basis(_abi.ptr(w.contiguous()), c2, win, self.hop_size,
-                                                      _abi.ptr(packed), _abi.stream_ptr()))
+            with torch.cuda.device(w.device):
+                _abi.check(_abi.lib().se_istft_pack_basis(_abi.ptr(w.contiguous()), c2, win, self.hop_size,
+                                                          _abi.ptr(packed), _abi.stream_ptr()))
             self._packed, self._packed_key = packed, key
         return self._packed
 

@@ -80,9 +80,10 @@ class ComplexConv(_abi.InvalidatesCaches, nn.Module):
             if rc.bias is not None:
                 br, bi = rc.bias.detach().contiguous(), ic.bias.detach().contiguous()
                 bias = torch.empty((2 * co,), device=wr.device, dtype=torch.float32)
-            _abi.check(_abi.lib().se_cconv_pack_weight(
-                _abi.ptr(wr), _abi.ptr(wi), _abi.ptr(br), _abi.ptr(bi), co, ci, kh, kw,
-                int(self._transposed), _abi.ptr(packed), _abi.ptr(bias), _abi.stream_ptr()))
+            with torch.cuda.device(wr.device):      # the weights' device, not whatever device is current
+                _abi.check(_abi.lib().se_cconv_pack_weight(
+                    _abi.ptr(wr), _abi.ptr(wi), _abi.ptr(br), _abi.ptr(bi), co, ci, kh, kw,
+                    int(self._transposed), _abi.ptr(packed), _abi.ptr(bias), _abi.stream_ptr()))
             self._pack, self._pack_key = (packed, bias, co, ci, kh, kw), key
         return self._pack
 
@@ -129,8 +130,9 @@ class ComplexConv(_abi.InvalidatesCaches, nn.Module):
         ws_bytes = lib.se_cconv_workspace_bytes(B, c2, H, W, cout2, kh, kw, sh, sw,
                                                 int(transposed)) if self.engine != _abi.ENGINE_SIMT else 0
         ws = torch.empty((ws_bytes,), device=x.device, dtype=torch.uint8) if ws_bytes > 0 else None
-        _abi.check(fn(_abi.ptr(x), _abi.ptr(packed), _abi.ptr(bias), B, c2, H, W, cout2, kh, kw,
-                      sh, sw, ph, pw, _abi.ptr(y), Ho, Wo, self.engine, _abi.ptr(ws), ws_bytes, _abi.stream_ptr()))
+        with torch.cuda.device(x.device):
+            _abi.check(fn(_abi.ptr(x), _abi.ptr(packed), _abi.ptr(bias), B, c2, H, W, cout2, kh, kw,
+                          sh, sw, ph, pw, _abi.ptr(y), Ho, Wo, self.engine, _abi.ptr(ws), ws_bytes, _abi.stream_ptr()))
         return y
 
     def _out_size(self, H, W, kh, kw):
