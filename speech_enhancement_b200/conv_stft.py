@@ -237,6 +237,8 @@ class ConvSTFT(_abi.InvalidatesCaches, nn.Module):
         pad = self.pad if self.center else 0
         T = (L + 2 * pad - win) // self.hop_size + 1
         out = torch.empty((B, c2, T), device=x.device, dtype=torch.float32)
+        if B == 0:                                        # empty batch: nothing to launch (F.conv1d also returns [0, C2, T])
+            return out
         window = w[0, 0]                                  # row f = 0 of the real block is the analysis window
         eng = self._pick_engine('ConvSTFT', window, False, B > 0)
         with torch.cuda.device(x.device), _abi.stage('stft'):

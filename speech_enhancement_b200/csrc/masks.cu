@@ -252,13 +252,13 @@ __global__ void __launch_bounds__(256) pcm16_from_f32_kernel(const float* __rest
 }  // namespace se
 
 extern "C" int se_pcm16_to_f32(const int16_t* x, int64_t n, float* y, void* stream) {
-  SE_REQUIRE(x && y && n >= 0, "se_pcm16_to_f32: bad arguments");
+  SE_REQUIRE(n >= 0 && (n == 0 || (x && y)), "se_pcm16_to_f32: bad arguments");
   if (n == 0) return SE_OK;
   se::pcm16_to_f32_kernel<<<se::grid_1d(n), 256, 0, (cudaStream_t)stream>>>(x, y, n);
   return se::check_launch("se_pcm16_to_f32");
 }
 extern "C" int se_pcm16_from_f32(const float* x, int64_t n, int16_t* y, void* stream) {
-  SE_REQUIRE(x && y && n >= 0, "se_pcm16_from_f32: bad arguments");
+  SE_REQUIRE(n >= 0 && (n == 0 || (x && y)), "se_pcm16_from_f32: bad arguments");
   if (n == 0) return SE_OK;
   se::pcm16_from_f32_kernel<<<se::grid_1d(n), 256, 0, (cudaStream_t)stream>>>(x, y, n);
   return se::check_launch("se_pcm16_from_f32");
