@@ -24,7 +24,7 @@ path).  Rank 0 prints ONE JSON line (contract in the task statement):
                 ConvSTFT -> ConviSTFT round-trip sweep (4 s x 256, 60 s x 8; both framings)
 The model timed on the GPU is the reference's own class (oracle/_ref, unmodified) bound to this package by
 dropin.install() + dropin.accelerate() when oracle/_ref is staged, else the package's host model
-(speech_enhancement_b200.callers); `config.gpu_model` says which.
+(speech_enhancement_b200.callers); `config.gpu_path` says which.
 `--impl reference` times the CPU arm alone on all host threads, same metric / unit / config.
 """
 import argparse
@@ -202,7 +202,7 @@ def cpu_kind_text(kind):
             if kind == 'reference' else 'torch-CPU restatement of the reference path (oracle port)') + ', flush-denormal on'
 
 
-def config_dict(key, batch, n_gpus, gpu_model=None):
+def config_dict(key, batch, n_gpus, gpu_path=None):
     m = MODELS[key]
     win, hop, fft = m['stft']
     d = {'workload': f'{m["name"]} forward (win {win} / hop {hop} / fft {fft}), {batch} x 4 s 16 kHz utterances '
@@ -211,8 +211,8 @@ def config_dict(key, batch, n_gpus, gpu_model=None):
          'parallelism': f'utterance-sharded x{n_gpus}, no data-path collective',
          'l2_policy': f'per-step activation working set (>= {m["act_mb"]} MB/utt) exceeds the 126 MB L2; '
                       'inputs rotate over 3 buffers'}
-    if gpu_model:
-        d['gpu_model'] = gpu_model
+    if gpu_path:
+        d['gpu_path'] = gpu_path
     return d
 
 
@@ -445,7 +445,7 @@ def bench_inference(key, B, steps, warmup, D, full=True, with_graph=False):
            'value': audio_s / (ms / 1e3), 'unit': UNIT, 'ms_per_step': ms / steps,
            'e2e': {'value': audio_s / (ms_e2e / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': B * L * 4 * D.world,
                    'd2h_bytes_per_step': B * out_len * 4 * D.world, 'ms_per_step': ms_e2e / steps},
-           'gpu_launches': int(launches), 'per_gpu_batch': B, 'n_gpus': D.world, 'gpu_model': gpu_what}
+           'gpu_launches': int(launches), 'per_gpu_batch': B, 'n_gpus': D.world, 'gpu_path': gpu_what}
     if ms_e2e16 is not None:
         res['e2e_pcm16'] = {'value': audio_s / (ms_e2e16 / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': B * L * 2 * D.world,
                             'd2h_bytes_per_step': B * out_len * 2 * D.world, 'ms_per_step': ms_e2e16 / steps,
@@ -638,7 +638,7 @@ def bench_train(steps, warmup, D, full=True):
                        f'x 4 s split {nb} per GPU, bucketed allreduce of the flat gradient ({grad_bytes / 1e6:.1f} MB) '
                        'on a side stream overlapped with backward',
            'metric': m['metric'], 'value': audio_s / (ms / 1e3), 'unit': UNIT, 'ms_per_step': ms / steps,
-           'scaling': 'strong', 'global_batch': GB, 'per_gpu_batch': nb, 'n_gpus': D.world, 'gpu_model': gpu_what,
+           'scaling': 'strong', 'global_batch': GB, 'per_gpu_batch': nb, 'n_gpus': D.world, 'gpu_path': gpu_what,
            'e2e': {'value': audio_s / (ms_e2e / 1e3), 'unit': UNIT, 'h2d_bytes_per_step': 2 * nb * L * 4 * D.world,
                    'd2h_bytes_per_step': 4 * D.world, 'ms_per_step': ms_e2e / steps},
            'gpu_launches': int(launches), 'clocks': clocks,
@@ -778,7 +778,7 @@ def run_ours(args):
                'sample': f'one CARN step at 4 x 4 s ({cpu_sec:.2f} s); ' + cpu_kind_text(kind)}
         cfg = {'workload': head['workload'], 'global_batch': head['global_batch'], 'per_gpu_batch': head['per_gpu_batch'],
                'parallelism': f'data-parallel x{D.world}, NCCL allreduce of the flat gradient',
-               'l2_policy': 'inputs rotate over 3 buffers; activations exceed L2', 'gpu_model': head['gpu_model']}
+               'l2_policy': 'inputs rotate over 3 buffers; activations exceed L2', 'gpu_path': head['gpu_path']}
         scaling, dtype = 'strong', 'f32'
     else:
         v1, cores, s1, kind = time_cpu_forward(key, 1, iters=5, warmup=1)
@@ -788,7 +788,7 @@ def run_ours(args):
                'batch1': {'value': v1, 'latency_ms': s1 * 1e3}, 'batch8': {'value': v8, 'ms': s8 * 1e3},
                'sample': f'{nb} x 4 s utterances (the better of batch 1, median of 5, and batch 8, median of 3); '
                          + cpu_kind_text(kind)}
-        cfg = config_dict(key, args.batch, D.world, head['gpu_model'])
+        cfg = config_dict(key, args.batch, D.world, head['gpu_path'])
         scaling, dtype = 'weak', 'f32 (bf16x3 split operands, fp32 accumulate)'
     line = {'metric': m['metric'], 'value': head['value'], 'unit': UNIT, 'n_gpus': D.world, 'steps': args.steps,
             'warmup': max(args.warmup, 3), 'ms_per_step': head['ms_per_step'], 'higher_is_better': True,
